@@ -1,0 +1,26 @@
+#!/usr/bin/env bash
+# TEST INFRASTRUCTURE. Builds oracle/_ref/libref_oracle.so from the reference sources WHERE THEY
+# LIE under /root/reference (nothing is copied into the repo; outputs only into oracle/_ref/, which
+# is git-ignored but travels to the GPU box). Recipe follows SURVEY.md Appendix B:
+#   - RayTracing/BVH.cpp compiled verbatim (Linux pch stand-in, two empty Assimp stubs, a case shim)
+#   - RayTracing/main_raytracing.cu compiled as host C++ after ONE mechanical edit (the <<<>>> launch)
+#   - cuRAND XORWOW from the toolkit's own header, host-side
+# The reference's own build system (MSBuild/vcpkg) is not run.
+set -euo pipefail
+HERE="$(cd "$(dirname "$0")" && pwd)"
+R="${REFERENCE_ROOT:-/root/reference}"
+OUT="$HERE/_ref"
+if [ ! -d "$R/RayTracing" ]; then echo "build_ref: $R not present - keeping prebuilt $OUT" >&2; exit 0; fi
+mkdir -p "$OUT"
+CUDA_INC="${CUDA_HOME:-/usr/local/cuda}/include"
+INC="-I$R -I$R/include -I$R/Common -I$CUDA_INC -DGLM_ENABLE_EXPERIMENTAL -I$HERE/ref_shim"
+# -ffp-contract=off: the oracle's arithmetic is plain IEEE mul/add (no FMA) - DESIGN.md "contraction policy"
+CXXFLAGS="-std=c++20 -O2 -w -fPIC -fopenmp -ffp-contract=off"
+g++ $CXXFLAGS $INC -include "$HERE/ref_shim/pch_linux.h" -c "$R/RayTracing/BVH.cpp" -o "$OUT/bvh_ref.o"
+sed 's/raytracing_kernel_main<<<Dg, Db>>>(render_data);/(void)Dg; (void)render_data;/' \
+    "$R/RayTracing/main_raytracing.cu" > "$OUT/rt_host.inc"
+g++ $CXXFLAGS $INC -I"$R/RayTracing" -DRT_HOST_SRC="\"$OUT/rt_host.inc\"" \
+    -c "$HERE/ref_shim/ref_api.cpp" -o "$OUT/ref_api.o"
+g++ -shared -fopenmp -o "$OUT/libref_oracle.so" "$OUT/ref_api.o" "$OUT/bvh_ref.o"
+rm -f "$OUT/rt_host.inc" "$OUT"/*.o
+echo "built $OUT/libref_oracle.so"

@@ -1,0 +1,86 @@
+// Device layout of the acceleration structure ("GPUScene upload re-layout", north-star item 1).
+//
+// The reference keeps 32-B nodes that name ONE box each, a u32 face-index permutation, 16-B faces
+// and 32-B vertices: a triangle test chases index -> face -> 3 vertices = 116 B through three
+// dependent loads (RayTracing/main_raytracing.cu:53-56). Here the SAME topology (same leaves, same
+// leaf contents, same order of slots as BVH.cpp's face_indices) is stored as
+//
+//   WideNode (64 B, 4 x 128-bit loads): the boxes of BOTH children of a reference inner node plus
+//            two child references, so one pop tests two boxes and orders them near-first;
+//   TriRecord (48 B, 3 x 128-bit loads) per BVH slot: v0, e1 = v1-v0, e2 = v2-v0 pre-gathered
+//            (bit-identical to what glm::intersectRayTriangle computes first, intersect.inl:38-39),
+//            with the face id and the owning reference leaf in the spare lanes;
+//   ShadeRecord (48 B) per slot: the three vertex normals and the material index, read once per hit.
+//
+// Child reference (u32): bit31 = 0 -> index of a WideNode; bit31 = 1 -> leaf:
+//   bits 27..30 = prim_count-1 (<= 16 prims), bits 0..26 = first slot. 0xFFFFFFFF = stack sentinel.
+// Reference leaves with more than `fat_leaf_threshold` prims (BVH.cpp never bounds leaf size; the
+// bunny scene has one of 345) keep their exact box in the parent and get a private sub-tree of
+// WideNodes over their own slots with conservatively inflated boxes (leaf contents unchanged).
+#pragma once
+#include <cstdint>
+#include <vector>
+#include "rt_types.h"
+
+#define RT_LEAF_BIT 0x80000000u
+#define RT_SENTINEL 0xFFFFFFFFu
+#define RT_MAX_LEAF_PRIMS 16u
+#define RT_STACK_SIZE 64
+
+struct RtFloat4 { float x, y, z, w; };
+
+struct alignas(64) WideNode
+{
+    RtFloat4 a;   // lo0.x lo0.y lo0.z hi0.x
+    RtFloat4 b;   // hi0.y hi0.z lo1.x lo1.y
+    RtFloat4 c;   // lo1.z hi1.x hi1.y hi1.z
+    uint32_t child[2];
+    uint32_t pad[2];
+};
+
+struct alignas(16) TriRecord
+{
+    float v0[3]; uint32_t face_id;
+    float e1[3]; uint32_t ref_leaf;   // index of the reference leaf node (for the exact box re-check)
+    float e2[3]; uint32_t orig_slot; // slot before any fat-leaf permutation (reference visiting order)
+};
+
+struct alignas(16) ShadeRecord
+{
+    float n0[3]; uint32_t material;
+    float n1[3]; uint32_t pad0;
+    float n2[3]; uint32_t pad1;
+};
+
+// Host-side result of the re-layout (accel_build.cpp); uploaded verbatim.
+struct AccelHost
+{
+    std::vector<WideNode> wide;        // wide[0] is the root (unless root_ref is a leaf)
+    std::vector<TriRecord> tris;       // one per BVH slot
+    std::vector<ShadeRecord> shade;    // one per BVH slot
+    uint32_t root_ref = RT_SENTINEL;
+    uint32_t ref_leaf_count = 0, fat_leaf_count = 0, wide_depth = 0, ref_depth = 0;
+};
+
+// Returns 0, or a negative RT_E_* (include/b200rt.h).
+int BuildAccelHost(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* face_indices,
+                   const RtFace* faces, uint32_t face_count, const RtVertex* vertices, uint32_t vertex_count,
+                   uint32_t fat_leaf_threshold, AccelHost& out);
+
+// Device-side view passed to kernels by value.
+struct AccelView
+{
+    const WideNode* wide;
+    const TriRecord* tris;
+    const ShadeRecord* shade;
+    const RtBVHNode* ref_nodes;  // device copy of the reference nodes (exact leaf boxes, reference-order kernel)
+    uint32_t root_ref;
+    uint32_t node_count;
+};
+
+struct RtAccel
+{
+    AccelView view{};
+    uint64_t device_bytes = 0;
+    uint32_t wide_count = 0, slot_count = 0, ref_leaf_count = 0, fat_leaf_count = 0, wide_depth = 0, ref_depth = 0;
+};

@@ -1,0 +1,182 @@
+// Host re-layout of the reference BVH into WideNode / TriRecord / ShadeRecord arrays (accel.h).
+// Compiled with -ffp-contract=off: e1/e2 must equal the fp32 differences the reference computes.
+#include "accel.h"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include "b200rt.h"
+
+namespace
+{
+    struct Box { float lo[3], hi[3]; };
+
+    inline Box EmptyBox() { return Box{ { 1e30f, 1e30f, 1e30f }, { -1e30f, -1e30f, -1e30f } }; }
+    inline void Grow(Box& b, const float* p) { for (int k = 0; k < 3; k++) { b.lo[k] = std::min(b.lo[k], p[k]); b.hi[k] = std::max(b.hi[k], p[k]); } }
+    inline void Grow(Box& b, const Box& o) { for (int k = 0; k < 3; k++) { b.lo[k] = std::min(b.lo[k], o.lo[k]); b.hi[k] = std::max(b.hi[k], o.hi[k]); } }
+    inline float HalfArea(const Box& b)
+    {
+        const float x = b.hi[0] - b.lo[0], y = b.hi[1] - b.lo[1], z = b.hi[2] - b.lo[2];
+        return x * y + y * z + z * x;
+    }
+    inline Box FromNode(const RtBVHNode& n) { return Box{ { n.bounds_min.x, n.bounds_min.y, n.bounds_min.z }, { n.bounds_max.x, n.bounds_max.y, n.bounds_max.z } }; }
+
+    // Sub-tree boxes have no reference counterpart: they only have to be supersets. Inflate generously so
+    // that any ray the (rounding-afflicted) triangle test accepts also passes the box (DESIGN.md "fat leaves").
+    inline Box Inflate(const Box& b)
+    {
+        float ext = 0, mag = 0;
+        for (int k = 0; k < 3; k++) { ext = std::max(ext, b.hi[k] - b.lo[k]); mag = std::max(mag, std::max(std::fabs(b.lo[k]), std::fabs(b.hi[k]))); }
+        const float pad = 0.01f * ext + 1e-4f * mag + 1e-6f;
+        Box r = b;
+        for (int k = 0; k < 3; k++) { r.lo[k] -= pad; r.hi[k] += pad; }
+        return r;
+    }
+
+    inline uint32_t LeafRef(uint32_t first, uint32_t count) { return RT_LEAF_BIT | ((count - 1u) << 27) | first; }
+
+    inline void SetChildBox(WideNode& w, int which, const Box& b)
+    {
+        if (which == 0) { w.a = { b.lo[0], b.lo[1], b.lo[2], b.hi[0] }; w.b.x = b.hi[1]; w.b.y = b.hi[2]; }
+        else { w.b.z = b.lo[0]; w.b.w = b.lo[1]; w.c = { b.lo[2], b.hi[0], b.hi[1], b.hi[2] }; }
+    }
+
+    struct Builder
+    {
+        const RtBVHNode* nodes; uint32_t node_count; uint32_t threshold;
+        AccelHost& out;
+        std::vector<Box> slot_box;      // per slot, for sub-trees
+        std::vector<float> slot_centroid;
+        int error = 0;
+
+        Box SlotBox(uint32_t s) const
+        {
+            const TriRecord& t = out.tris[s];
+            Box b = EmptyBox();
+            float v1[3], v2[3];
+            for (int k = 0; k < 3; k++) { v1[k] = t.v0[k] + t.e1[k]; v2[k] = t.v0[k] + t.e2[k]; }
+            Grow(b, t.v0); Grow(b, v1); Grow(b, v2);
+            // v0+e1 may differ from v1 by an ulp; the sub-tree boxes are inflated far beyond that
+            return b;
+        }
+
+        // SAH sweep sub-tree over slots [first, first+count); permutes tris/shade inside the range.
+        uint32_t BuildSub(uint32_t first, uint32_t count, uint32_t depth, Box& bounds_out)
+        {
+            Box bounds = EmptyBox();
+            for (uint32_t s = first; s < first + count; s++) Grow(bounds, SlotBox(s));
+            bounds_out = bounds;
+            if (count <= 4) return LeafRef(first, count);
+
+            std::vector<uint32_t> order(count);
+            std::vector<Box> boxes(count);
+            std::vector<float> right_area(count);
+            float best_cost = 3.4e38f; int best_axis = -1; uint32_t best_split = 0;
+            for (int axis = 0; axis < 3; axis++)
+            {
+                for (uint32_t i = 0; i < count; i++) { order[i] = first + i; }
+                std::vector<float> cen(count);
+                for (uint32_t i = 0; i < count; i++) { const Box b = SlotBox(first + i); cen[i] = b.lo[axis] + b.hi[axis]; }
+                std::vector<uint32_t> idx(count);
+                for (uint32_t i = 0; i < count; i++) idx[i] = i;
+                std::stable_sort(idx.begin(), idx.end(), [&](uint32_t a, uint32_t b) { return cen[a] < cen[b]; });
+                Box acc = EmptyBox();
+                for (uint32_t i = count; i-- > 0;) { Grow(acc, SlotBox(first + idx[i])); right_area[i] = HalfArea(acc); }
+                acc = EmptyBox();
+                for (uint32_t i = 0; i + 1 < count; i++)
+                {
+                    Grow(acc, SlotBox(first + idx[i]));
+                    const float cost = HalfArea(acc) * float(i + 1) + right_area[i + 1] * float(count - i - 1);
+                    if (cost < best_cost) { best_cost = cost; best_axis = axis; best_split = i + 1; }
+                }
+            }
+            // apply the best permutation
+            {
+                std::vector<float> cen(count);
+                for (uint32_t i = 0; i < count; i++) { const Box b = SlotBox(first + i); cen[i] = b.lo[best_axis] + b.hi[best_axis]; }
+                std::vector<uint32_t> idx(count);
+                for (uint32_t i = 0; i < count; i++) idx[i] = i;
+                std::stable_sort(idx.begin(), idx.end(), [&](uint32_t a, uint32_t b) { return cen[a] < cen[b]; });
+                std::vector<TriRecord> t(count); std::vector<ShadeRecord> sh(count);
+                for (uint32_t i = 0; i < count; i++) { t[i] = out.tris[first + idx[i]]; sh[i] = out.shade[first + idx[i]]; }
+                std::copy(t.begin(), t.end(), out.tris.begin() + first);
+                std::copy(sh.begin(), sh.end(), out.shade.begin() + first);
+            }
+            const uint32_t w = (uint32_t)out.wide.size();
+            out.wide.push_back(WideNode{});
+            out.wide_depth = std::max(out.wide_depth, depth + 1);
+            Box b0, b1;
+            const uint32_t c0 = BuildSub(first, best_split, depth + 1, b0);
+            const uint32_t c1 = BuildSub(first + best_split, count - best_split, depth + 1, b1);
+            WideNode& node = out.wide[w];
+            SetChildBox(node, 0, Inflate(b0)); SetChildBox(node, 1, Inflate(b1));
+            node.child[0] = c0; node.child[1] = c1;
+            return w;
+        }
+
+        // Child reference for reference node `n` (whose exact box the PARENT stores).
+        uint32_t Emit(uint32_t n, uint32_t depth)
+        {
+            if (n >= node_count) { error = RT_E_INVALID; return RT_SENTINEL; }
+            const RtBVHNode& node = nodes[n];
+            out.ref_depth = std::max(out.ref_depth, depth);
+            if (node.prim_count > 0)
+            {
+                out.ref_leaf_count++;
+                if ((uint64_t)node.first_index + node.prim_count > out.tris.size()) { error = RT_E_INVALID; return RT_SENTINEL; }
+                for (uint32_t s = node.first_index; s < node.first_index + node.prim_count; s++) out.tris[s].ref_leaf = n;
+                if (node.prim_count <= threshold) return LeafRef(node.first_index, node.prim_count);
+                out.fat_leaf_count++;
+                Box unused;
+                return BuildSub(node.first_index, node.prim_count, depth, unused);
+            }
+            if (depth > 4096) { error = RT_E_DEPTH; return RT_SENTINEL; }
+            const uint32_t w = (uint32_t)out.wide.size();
+            out.wide.push_back(WideNode{});
+            out.wide_depth = std::max(out.wide_depth, depth + 1);
+            const uint32_t l = node.first_index, r = node.first_index + 1;
+            if (r >= node_count) { error = RT_E_INVALID; return RT_SENTINEL; }
+            const uint32_t c0 = Emit(l, depth + 1);
+            const uint32_t c1 = Emit(r, depth + 1);
+            WideNode& wn = out.wide[w];
+            SetChildBox(wn, 0, FromNode(nodes[l])); SetChildBox(wn, 1, FromNode(nodes[r]));  // exact reference boxes
+            wn.child[0] = c0; wn.child[1] = c1;
+            return w;
+        }
+    };
+}
+
+int BuildAccelHost(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* face_indices,
+                   const RtFace* faces, uint32_t face_count, const RtVertex* vertices, uint32_t vertex_count,
+                   uint32_t fat_leaf_threshold, AccelHost& out)
+{
+    if (!nodes || !node_count || !face_indices || !faces || !vertices || !face_count) return RT_E_INVALID;
+    if (face_count >= (1u << 27)) return RT_E_INVALID;
+    if (fat_leaf_threshold == 0) fat_leaf_threshold = 8;
+    if (fat_leaf_threshold > RT_MAX_LEAF_PRIMS) fat_leaf_threshold = RT_MAX_LEAF_PRIMS;
+
+    out = AccelHost();
+    out.tris.resize(face_count); out.shade.resize(face_count);
+    for (uint32_t s = 0; s < face_count; s++)
+    {
+        const uint32_t id = face_indices[s];
+        if (id >= face_count) return RT_E_INVALID;
+        const RtFace& f = faces[id];
+        if (f.v0 >= vertex_count || f.v1 >= vertex_count || f.v2 >= vertex_count) return RT_E_INVALID;
+        const RtVertex& a = vertices[f.v0]; const RtVertex& b = vertices[f.v1]; const RtVertex& c = vertices[f.v2];
+        TriRecord& t = out.tris[s];
+        t.v0[0] = a.position.x; t.v0[1] = a.position.y; t.v0[2] = a.position.z; t.face_id = id;
+        t.e1[0] = b.position.x - a.position.x; t.e1[1] = b.position.y - a.position.y; t.e1[2] = b.position.z - a.position.z; t.ref_leaf = 0;
+        t.e2[0] = c.position.x - a.position.x; t.e2[1] = c.position.y - a.position.y; t.e2[2] = c.position.z - a.position.z; t.orig_slot = s;
+        ShadeRecord& h = out.shade[s];
+        h.n0[0] = a.normal.x; h.n0[1] = a.normal.y; h.n0[2] = a.normal.z; h.material = f.material;
+        h.n1[0] = b.normal.x; h.n1[1] = b.normal.y; h.n1[2] = b.normal.z; h.pad0 = 0;
+        h.n2[0] = c.normal.x; h.n2[1] = c.normal.y; h.n2[2] = c.normal.z; h.pad1 = 0;
+    }
+    Builder builder{ nodes, node_count, fat_leaf_threshold, out, {}, {}, 0 };
+    out.wide.reserve(node_count / 2 + 16);
+    out.root_ref = builder.Emit(0, 0);
+    if (builder.error) return builder.error;
+    if (out.wide_depth + 2 > RT_STACK_SIZE || out.ref_depth + 2 > RT_STACK_SIZE) return RT_E_DEPTH;
+    if (out.wide.empty()) out.wide.push_back(WideNode{});  // keep the device array non-empty
+    return 0;
+}

@@ -1,0 +1,31 @@
+// Shared between the C-ABI translation units (capi.cu, capi_render.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <map>
+#include <mutex>
+#include <string>
+#include "accel.h"
+#include "b200rt.h"
+#include "kernels.h"
+
+namespace rt_internal
+{
+    inline thread_local std::string g_error;
+    inline std::mutex g_mutex;
+    inline std::map<const void*, RtAccel*> g_bound;  // gpu_bvh_nodes -> accel (raytracing_process lookup)
+
+    inline int Fail(int code, const std::string& msg) { g_error = msg; return code; }
+    inline int CudaFail(cudaError_t e, const char* what) { return Fail(RT_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e)); }
+
+    inline SceneView MakeSceneView(const RtGPUScene* s)
+    {
+        SceneView v{};
+        if (!s) return v;
+        v.spheres = s->gpu_spheres; v.materials = s->gpu_materials;
+        v.sphere_count = s->gpu_spheres ? s->sphere_count : 0; v.material_count = s->material_count;
+        v.rng_state = s->rng_state; v.env_tex = (cudaTextureObject_t)s->environment_cubemap_tex;
+        v.camera = s->camera;
+        return v;
+    }
+}
+#define RT_CUDA(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return rt_internal::CudaFail(e_, #call); } while (0)

@@ -1,0 +1,180 @@
+// Path-trace kernels: raytracing_kernel_main (RayTracing/main_raytracing.cu:162-200) rebuilt for
+// sm_100a. Compiled with -fmad=false.
+//
+// variant 0 "regenerating megakernel": one lane owns one pixel for the whole launch, but the
+//   reference's nested `for sample { for bounce { trace; shade } }` is flattened into ONE loop whose
+//   body is exactly one closest-hit query: a lane whose path ended starts its next sample in the same
+//   iteration, so every lane of a warp is inside the traversal loop until its samples run out
+//   (SIMT efficiency no longer limited by the longest path per sample). Per pixel the order of RNG
+//   draws and fp32 operations is the reference's, so the stream and the image are reproduced.
+//   The XORWOW state lives in registers for the launch (reference: 24-B global RMW per draw).
+#include <cmath>
+#include "shade.cuh"
+
+__device__ __forceinline__ void camera_ray_pt(const RtCamera& cam, float u, float v, Vec3& o, Vec3& d)
+{
+    o = mk3(cam.origin.x, cam.origin.y, cam.origin.z);
+    const Vec3 h = mk3(cam.horizontal.x, cam.horizontal.y, cam.horizontal.z), w = mk3(cam.vertical.x, cam.vertical.y, cam.vertical.z);
+    const Vec3 llc = mk3(cam.lower_left_corner.x, cam.lower_left_corner.y, cam.lower_left_corner.z);
+    d = ((llc + u * h) + v * w) - o;
+}
+
+struct FrameParams
+{
+    unsigned char* surface;
+    unsigned char* surface_last;
+    int width, height;
+    uint64_t pitch;
+    int frame_index, spp, max_bounces, blend_mode, write_last;
+    unsigned long long* ray_counter;
+    PathConsts consts;
+};
+
+// Final pixel write: main_raytracing.cu:195-199 (blend_mode 0) or sum accumulation (blend_mode 1).
+__device__ __forceinline__ void write_pixel(const FrameParams& P, int x, int y, Vec3 sum)
+{
+    float4* px = reinterpret_cast<float4*>(P.surface + (size_t)y * P.pitch) + x;
+    float4 out;
+    if (P.blend_mode == 0)
+    {
+        const float n = (float)P.spp;
+        const Vec3 mean = mk3(sum.x / n, sum.y / n, sum.z / n);
+        const float a = P.frame_index > 0 ? 1.0f / (float)(P.frame_index + 1) : 1.0f;
+        const float4 last = *(reinterpret_cast<const float4*>(P.surface_last + (size_t)y * P.pitch) + x);
+        out = make_float4(mix1(last.x, mean.x, a), mix1(last.y, mean.y, a), mix1(last.z, mean.z, a), 1.0f);
+    }
+    else
+    {
+        const float4 cur = *px;
+        out = make_float4(cur.x + sum.x, cur.y + sum.y, cur.z + sum.z, cur.w + (float)P.spp);
+    }
+    *px = out;
+    if (P.write_last) *(reinterpret_cast<float4*>(P.surface_last + (size_t)y * P.pitch) + x) = out;
+}
+
+__global__ void __launch_bounds__(256) pathtrace_megakernel(AccelView A, SceneView S, FrameParams P)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int x = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+    const int y = blockIdx.y * 16 + (warp >> 1) * 4 + (lane >> 3);
+    const bool active = x < P.width && y < P.height;
+    unsigned rays = 0;
+    if (active)
+    {
+        RtRngState* state = S.rng_state + (size_t)y * P.width + x;  // GPUScene::GetRNGForPixel, GPUScene.h:95
+        Xorwow rng; rng.load(state);
+        Vec3 sum = mk3(0, 0, 0);
+        PathState ps;
+        int sample = 0, bounce = 0;
+        bool fresh = true;
+        while (sample < P.spp)
+        {
+            if (fresh)
+            {   // main_raytracing.cu:190-191; jitter draws x first, then y
+                const float jx = rng.uniform(), jy = rng.uniform();
+                const float u = ((float)x + jx) / (float)P.width, v = ((float)y + jy) / (float)P.height;
+                camera_ray_pt(S.camera, u, v, ps.o, ps.d);
+                ps.throughput = mk3(1, 1, 1); ps.radiance = mk3(0, 0, 0);
+                bounce = 0; fresh = false;
+            }
+            const Vec3 nd = normalize3(ps.d);
+            HitRecord h; h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
+            sphere_tests(S.spheres, S.sphere_count, ps.o, nd, h);
+            trace_wide<false>(A, ps.o, ps.d, nd, h);
+            rays++;
+            bool alive;
+            if (h.id != RT_MISS_ID) alive = shade_hit(A, S, h, ps, rng) && (++bounce < P.max_bounces);
+            else { if (S.env_tex) shade_miss(S, P.consts, ps); alive = false; }
+            if (!alive) { sum = sum + ps.radiance; sample++; fresh = true; }
+        }
+        rng.store(state);
+        write_pixel(P, x, y, sum);
+    }
+    if (P.ray_counter)
+    {
+        for (int o = 16; o; o >>= 1) rays += __shfl_xor_sync(0xffffffffu, rays, o);
+        if (lane == 0 && rays) atomicAdd(P.ray_counter, (unsigned long long)rays);
+    }
+}
+
+cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, const RtProcessParams& p, cudaStream_t stream)
+{
+    FrameParams P;
+    P.surface = (unsigned char*)p.surface; P.surface_last = (unsigned char*)p.surface_last_frame;
+    P.width = p.width; P.height = p.height; P.pitch = p.pitch; P.frame_index = p.frame_index;
+    P.spp = p.samples_per_launch; P.max_bounces = p.max_bounces; P.blend_mode = p.blend_mode; P.write_last = p.write_last_frame;
+    P.ray_counter = p.d_ray_counter;
+    {   // glm quat(vec3(0, PI, 0)), type_quat.inl:204-213, in host fp32 like the oracle
+        const float PI = 3.1415926536f;
+        const float cx = std::cos(0.0f * 0.5f), cy = std::cos(PI * 0.5f), cz = std::cos(0.0f * 0.5f);
+        const float sx = std::sin(0.0f * 0.5f), sy = std::sin(PI * 0.5f), sz = std::sin(0.0f * 0.5f);
+        P.consts.qw = cx * cy * cz + sx * sy * sz;
+        P.consts.qx = sx * cy * cz - cx * sy * sz;
+        P.consts.qy = cx * sy * cz + sx * cy * sz;
+        P.consts.qz = cx * cy * sz - sx * sy * cz;
+    }
+    const dim3 grid((p.width + 15) / 16, (p.height + 15) / 16), block(256);
+    pathtrace_megakernel<<<grid, block, 0, stream>>>(accel, scene, P);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// Ambient-occlusion stress (BASELINE.json config 3): incoherent rays from the reference's own diffuse
+// lobe and origin offset (main_raytracing.cu:129,135). Flattened like the megakernel: one query per
+// loop iteration (iteration 0 = the pixel-centre primary ray).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ambient_occlusion_kernel(AccelView A, SceneView S, int width, int height, int ao_rays,
+                                                                float* __restrict__ out, unsigned long long* ray_counter)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int x = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+    const int y = blockIdx.y * 16 + (warp >> 1) * 4 + (lane >> 3);
+    unsigned rays = 0;
+    if (x < width && y < height)
+    {
+        RtRngState* state = S.rng_state + (size_t)y * width + x;
+        Xorwow rng; rng.load(state);
+        Vec3 o, d; camera_ray_pt(S.camera, ((float)x + 0.5f) / (float)width, ((float)y + 0.5f) / (float)height, o, d);
+        Vec3 base = o, normal = mk3(0, 0, 0);
+        int unoccluded = 0, total = 0;
+        for (int k = 0; k <= ao_rays; k++)
+        {
+            const Vec3 nd = normalize3(d);
+            HitRecord h; h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
+            sphere_tests(S.spheres, S.sphere_count, o, nd, h);
+            trace_wide<false>(A, o, d, nd, h);
+            rays++;
+            if (k == 0)
+            {
+                if (h.id == RT_MISS_ID) break;
+                const Vec3 position = o + nd * h.t;
+                if (h.id & RT_SPHERE_ID_BIT) { const float4 s = ldg4(&S.spheres[h.slot]); normal = (position - mk3(s.x, s.y, s.z)) / s.w; }
+                else
+                {
+                    const ShadeRecord* sr = A.shade + h.slot;
+                    const float4 n0 = ldg4(sr), n1 = ldg4(reinterpret_cast<const char*>(sr) + 16), n2 = ldg4(reinterpret_cast<const char*>(sr) + 32);
+                    normal = normalize3((mk3(n0.x, n0.y, n0.z) * h.bu + mk3(n1.x, n1.y, n1.z) * h.bv) + mk3(n2.x, n2.y, n2.z) * (1.0f - h.bu - h.bv));
+                    if (dot3(nd, normal) >= 0.0f) normal = -normal;
+                }
+                base = position + normal * 0.01f;
+            }
+            else { total++; if (h.id == RT_MISS_ID) unoccluded++; }
+            o = base; d = normalize3(normal + rng.point_on_sphere());
+        }
+        rng.store(state);
+        out[(size_t)y * width + x] = total ? (float)unoccluded / (float)total : 1.0f;
+    }
+    if (ray_counter)
+    {
+        for (int o2 = 16; o2; o2 >>= 1) rays += __shfl_xor_sync(0xffffffffu, rays, o2);
+        if (lane == 0 && rays) atomicAdd(ray_counter, (unsigned long long)rays);
+    }
+}
+
+cudaError_t LaunchAmbientOcclusion(const AccelView& accel, const SceneView& scene, int width, int height, int ao_rays,
+                                   float* d_ao, unsigned long long* d_ray_counter, cudaStream_t stream)
+{
+    const dim3 grid((width + 15) / 16, (height + 15) / 16), block(256);
+    ambient_occlusion_kernel<<<grid, block, 0, stream>>>(accel, scene, width, height, ao_rays, d_ao, d_ray_counter);
+    return cudaGetLastError();
+}

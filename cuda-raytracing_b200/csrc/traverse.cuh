@@ -1,0 +1,217 @@
+// Closest-hit traversal for sm_100a. This TU is compiled with -fmad=false: every `a*b+c` below is
+// two IEEE roundings, exactly like the host-compiled reference the parity tests compare against
+// (DESIGN.md "contraction policy"); FMAs are written explicitly (fmaf) where parity does not hang
+// on them (conservative box tests).
+//
+// Result rule (BASELINE.json): min t over the triangles the reference would test, exact ties ->
+// lowest face id. Triangle arithmetic restates glm::intersectRayTriangle
+// (include/glm/gtx/intersect.inl:29-94) on the pre-gathered v0/e1/e2; the exact leaf-box test
+// restates Math::IntersectAABB (RayTracing/Math.h:50-61) as BVHRayHit calls it
+// (RayTracing/main_raytracing.cu:46: UNNORMALISED direction, normalised-units length).
+#pragma once
+#include <cfloat>
+#include <cstdint>
+#include "accel.h"
+
+struct Vec3 { float x, y, z; };
+
+__device__ __forceinline__ Vec3 mk3(float x, float y, float z) { Vec3 v; v.x = x; v.y = y; v.z = z; return v; }
+__device__ __forceinline__ Vec3 operator+(Vec3 a, Vec3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ Vec3 operator-(Vec3 a, Vec3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ Vec3 operator-(Vec3 a) { return mk3(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ Vec3 operator*(Vec3 a, Vec3 b) { return mk3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ Vec3 operator*(Vec3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ Vec3 operator*(float s, Vec3 a) { return mk3(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ Vec3 operator/(Vec3 a, float s) { return mk3(a.x / s, a.y / s, a.z / s); }
+// glm/detail/func_geometric.inl:48-54,68-78,82-89 ; func_exponential.inl:136-139
+__device__ __forceinline__ float dot3(Vec3 a, Vec3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ Vec3 cross3(Vec3 x, Vec3 y) { return mk3(x.y * y.z - y.y * x.z, x.z * y.x - y.z * x.x, x.x * y.y - y.x * x.y); }
+__device__ __forceinline__ Vec3 normalize3(Vec3 v) { return v * (1.0f / sqrtf(dot3(v, v))); }
+
+struct HitRecord
+{
+    float t;        // normalised-direction units; 1e30f = miss
+    uint32_t id;    // face id, RT_SPHERE_ID_BIT | sphere, or RT_MISS_ID
+    uint32_t slot;  // BVH slot of the winning triangle (ShadeRecord index)
+    uint32_t key;   // exact-tie key of the winner (face id, or original slot = reference leaf order)
+    float bu, bv;   // glm baryPosition.x / .y of the winner
+};
+
+__device__ __forceinline__ float4 ldg4(const void* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+
+// Math::IntersectAABB with the reference's operand roles. Order-independent use: ray_length = the
+// distance the BVH search STARTED with (sphere hit or 1e30).
+__device__ __forceinline__ bool exact_box(Vec3 o, Vec3 d, const RtBVHNode* node, float ray_length)
+{
+    const float4 q0 = ldg4(node);                                    // min.xyz max.x
+    const float4 q1 = ldg4(reinterpret_cast<const char*>(node) + 16);  // max.yz first count
+    const float tx1 = (q0.x - o.x) / d.x, tx2 = (q0.w - o.x) / d.x;
+    float tmin = fminf(tx1, tx2), tmax = fmaxf(tx1, tx2);
+    const float ty1 = (q0.y - o.y) / d.y, ty2 = (q1.x - o.y) / d.y;
+    tmin = fmaxf(tmin, fminf(ty1, ty2)); tmax = fminf(tmax, fmaxf(ty1, ty2));
+    const float tz1 = (q0.z - o.z) / d.z, tz2 = (q1.y - o.z) / d.z;
+    tmin = fmaxf(tmin, fminf(tz1, tz2)); tmax = fminf(tmax, fmaxf(tz1, tz2));
+    return tmax >= tmin && tmin < ray_length && tmax > 0;
+}
+
+// glm::intersectRayTriangle on a TriRecord. Returns true with (t, bu, bv) when GLM would.
+__device__ __forceinline__ bool tri_test(Vec3 o, Vec3 nd, float4 r0, float4 r1, float4 r2, float& t, float& bu, float& bv)
+{
+    const Vec3 v0 = mk3(r0.x, r0.y, r0.z), e1 = mk3(r1.x, r1.y, r1.z), e2 = mk3(r2.x, r2.y, r2.z);
+    const Vec3 p = cross3(nd, e2);
+    const float det = dot3(e1, p);
+    const Vec3 dist = o - v0;
+    const float u = dot3(dist, p);
+    const Vec3 perp = cross3(dist, e1);
+    const float v = dot3(nd, perp);
+    if (det > FLT_EPSILON)
+    {
+        if (u < 0.0f || u > det) return false;
+        if (v < 0.0f || (u + v) > det) return false;
+    }
+    else if (det < -FLT_EPSILON)
+    {
+        if (u > 0.0f || u < det) return false;
+        if (v > 0.0f || (u + v) < det) return false;
+    }
+    else return false;
+    const float inv_det = 1.0f / det;
+    t = dot3(e2, perp) * inv_det;
+    bu = u * inv_det; bv = v * inv_det;
+    return true;
+}
+
+// Candidate acceptance: main_raytracing.cu:62 (`distance >= best || distance < 0` rejects). The
+// reference keeps the FIRST-VISITED candidate on exact ties, which depends on traversal order; here
+// ties are resolved by an order-independent key: the face id (kTieById, BASELINE.json's rule for the
+// hit-id parity config) or the original BVH slot (= the reference's visiting order inside a leaf,
+// used by the path tracer so shading picks the same duplicate the reference does).
+__device__ __forceinline__ bool accept(float t, uint32_t key, const HitRecord& h)
+{
+    if (t > h.t || t < 0.0f) return false;
+    return t < h.t || (key < h.key && !(h.id & RT_SPHERE_ID_BIT));  // a sphere at the same t keeps the hit (:62, `>=`)
+}
+
+template <bool kLazyExactBox, bool kTieById>
+__device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, uint32_t count, Vec3 o, Vec3 d, Vec3 nd,
+                                           float start_length, HitRecord& h)
+{
+    const TriRecord* tr = A.tris + first;
+    for (uint32_t i = 0; i < count; i++)
+    {
+        const float4 r0 = ldg4(&tr[i]), r1 = ldg4(reinterpret_cast<const char*>(&tr[i]) + 16), r2 = ldg4(reinterpret_cast<const char*>(&tr[i]) + 32);
+        float t, bu, bv;
+        if (!tri_test(o, nd, r0, r1, r2, t, bu, bv)) continue;
+        const uint32_t id = __float_as_uint(r0.w);
+        const uint32_t key = kTieById ? id : __float_as_uint(r2.w);
+        if (!accept(t, key, h)) continue;
+        if (kLazyExactBox)
+        {   // the reference only tests this triangle if its leaf's box passes (main_raytracing.cu:46)
+            if (!exact_box(o, d, A.ref_nodes + __float_as_uint(r1.w), start_length)) continue;
+        }
+        h.t = t; h.id = id; h.slot = first + i; h.key = key; h.bu = bu; h.bv = bv;
+    }
+}
+
+// Product traversal: wide nodes, near-child-first, while-while, conservative box culls in
+// normalised units, exact leaf box re-check only on candidate hits.
+// `h` enters holding the sphere result (or a miss with t = 1e30).
+template <bool kTieById>
+__device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, Vec3 nd, HitRecord& h)
+{
+    const float start_length = h.t;
+    // reciprocal of the normalised direction; zero components -> huge finite (conservative)
+    const float big = 1e30f;
+    const float ix = nd.x != 0.0f ? 1.0f / nd.x : big, iy = nd.y != 0.0f ? 1.0f / nd.y : big, iz = nd.z != 0.0f ? 1.0f / nd.z : big;
+    const float kWiden = 1.0e-6f;
+
+    uint32_t stack[RT_STACK_SIZE];
+    int sp = 0;
+    stack[sp++] = RT_SENTINEL;
+    uint32_t node = A.root_ref;
+
+    while (node != RT_SENTINEL)
+    {
+        while (!(node & RT_LEAF_BIT))
+        {
+            const WideNode* w = A.wide + node;
+            const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32);
+            const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
+            // child 0
+            float t1 = (a.x - o.x) * ix, t2 = (a.w - o.x) * ix;
+            float mn0 = fminf(t1, t2), mx0 = fmaxf(t1, t2);
+            t1 = (a.y - o.y) * iy; t2 = (b.x - o.y) * iy;
+            mn0 = fmaxf(mn0, fminf(t1, t2)); mx0 = fminf(mx0, fmaxf(t1, t2));
+            t1 = (a.z - o.z) * iz; t2 = (b.y - o.z) * iz;
+            mn0 = fmaxf(mn0, fminf(t1, t2)); mx0 = fminf(mx0, fmaxf(t1, t2));
+            // child 1
+            t1 = (b.z - o.x) * ix; t2 = (c.y - o.x) * ix;
+            float mn1 = fminf(t1, t2), mx1 = fmaxf(t1, t2);
+            t1 = (b.w - o.y) * iy; t2 = (c.z - o.y) * iy;
+            mn1 = fmaxf(mn1, fminf(t1, t2)); mx1 = fminf(mx1, fmaxf(t1, t2));
+            t1 = (c.x - o.z) * iz; t2 = (c.w - o.z) * iz;
+            mn1 = fmaxf(mn1, fminf(t1, t2)); mx1 = fminf(mx1, fmaxf(t1, t2));
+            // widen (superset of the reference's divisions), cull against the current best
+            const float lo0 = fmaf(-kWiden, fabsf(mn0), mn0), hi0 = fmaf(kWiden, fabsf(mx0), mx0);
+            const float lo1 = fmaf(-kWiden, fabsf(mn1), mn1), hi1 = fmaf(kWiden, fabsf(mx1), mx1);
+            const bool hit0 = hi0 >= lo0 && lo0 <= h.t && hi0 > 0.0f;
+            const bool hit1 = hi1 >= lo1 && lo1 <= h.t && hi1 > 0.0f;
+            if (hit0 && hit1)
+            {
+                const bool swap = mn1 < mn0;
+                stack[sp++] = swap ? ch.x : ch.y;
+                node = swap ? ch.y : ch.x;
+            }
+            else if (hit0) node = ch.x;
+            else if (hit1) node = ch.y;
+            else node = stack[--sp];
+        }
+        if (node == RT_SENTINEL) break;
+        leaf_tests<true, kTieById>(A, node & 0x07FFFFFFu, ((node >> 27) & 0xFu) + 1u, o, d, nd, start_length, h);
+        node = stack[--sp];
+    }
+}
+
+// Reference-order traversal over the reference-layout nodes: right child first, exact box test at
+// every node against the CURRENT best (main_raytracing.cu:43-78). By-construction parity kernel.
+template <bool kTieById>
+__device__ __forceinline__ void trace_reference_order(const AccelView& A, Vec3 o, Vec3 d, Vec3 nd, HitRecord& h,
+                                                      uint32_t* nodes_popped = nullptr, uint32_t* tris_tested = nullptr)
+{
+    uint32_t stack[RT_STACK_SIZE];
+    int sp = 0;
+    stack[sp++] = 0;
+    while (sp)
+    {
+        const RtBVHNode* n = A.ref_nodes + stack[--sp];
+        if (nodes_popped) (*nodes_popped)++;
+        if (!exact_box(o, d, n, h.t)) continue;
+        const float4 q1 = ldg4(reinterpret_cast<const char*>(n) + 16);
+        const uint32_t first = __float_as_uint(q1.z), count = __float_as_uint(q1.w);
+        if (count)
+        {
+            if (tris_tested) (*tris_tested) += count;
+            leaf_tests<false, kTieById>(A, first, count, o, d, nd, 0.0f, h);
+        }
+        else { stack[sp++] = first; stack[sp++] = first + 1; }
+    }
+}
+
+// Spheres first, as GetRayHit does (main_raytracing.cu:89-103, glm intersect.inl:135-153).
+__device__ __forceinline__ void sphere_tests(const RtSphere* spheres, int count, Vec3 o, Vec3 nd, HitRecord& h)
+{
+    for (int i = 0; i < count; i++)
+    {
+        const float4 s = ldg4(&spheres[i]);  // position, radius
+        const Vec3 diff = mk3(s.x, s.y, s.z) - o;
+        const float t0 = dot3(diff, nd);
+        const float r2 = s.w * s.w;
+        const float d2 = dot3(diff, diff) - t0 * t0;
+        if (d2 > r2) continue;
+        const float t1 = sqrtf(r2 - d2);
+        const float t = t0 > t1 + FLT_EPSILON ? t0 - t1 : t0 + t1;
+        if (!(t > FLT_EPSILON)) continue;
+        if (t >= h.t) continue;
+        h.t = t; h.id = RT_SPHERE_ID_BIT | (uint32_t)i; h.slot = (uint32_t)i; h.key = 0;
+    }
+}

@@ -1,0 +1,122 @@
+"""CPU tests: data-model layout, host scene assembly and BVH topology against the reference
+(oracle/_ref = the reference's GPUScene.h / BVH.cpp / GLM compiled host-side) and the golden hashes."""
+import ctypes as C
+import hashlib
+import json
+import os
+
+import numpy as np
+
+import util
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def test_library_exports_every_declared_symbol(rt):
+    lib = rt.lib()
+    import re
+    declared = set()
+    for h in ("b200rt.h", "b200rt_host.h"):
+        text = open(os.path.join(util.ROOT, "include", h)).read()
+        declared |= set(re.findall(r"\b((?:rt_|raytracing_process|init_rng)\w*)\s*\(", text))
+    declared -= {"rt_last_error()"}
+    assert {"raytracing_process", "init_rng", "rt_process_ex", "rt_accel_create"} <= declared
+    for name in sorted(declared):
+        assert hasattr(lib, name), name
+    assert declared <= set(rt.SYMBOLS), declared - set(rt.SYMBOLS)
+
+
+def test_pod_layout_matches_reference_structs(rt, ref):
+    s = ref.lib().ref_sizeof
+    assert [s(i) for i in range(8)] == [32, 16, 32, 64, 32, 60, 136, 48]
+    assert (s(8), s(9), s(10)) == (72, 56, 64)          # GPUScene: camera, rng_state, env tex
+    assert (s(11), s(12), s(13)) == (4, 8, 24)          # GPUFace v2, v1 ; GPUBVHNode first_index
+    assert (s(14), s(15), s(16), s(17)) == (48, 16, 24, 48)
+    assert C.sizeof(rt.GPUScene) == 136 and rt.CAMERA.itemsize == 60
+
+
+def test_compute_entry_points_fail_loudly_without_device(rt):
+    if rt.lib().rt_device_count() > 0:
+        return
+    scene = rt.Scene()
+    scene.add_triangle((0, 0, 1), (1, 0, 1), (0, 1, 1), scene.add_material())
+    try:
+        scene.upload(None)
+    except rt.RtError as e:
+        assert "no CPU fallback" in str(e) or "CUDA" in str(e)
+    else:
+        raise AssertionError("upload must fail without a device")
+
+
+def test_scene_assembly_bitwise_vs_glm_build(rt, ref, bunny):
+    a = bunny["arrays"]
+    pos, nrm, idx, _ = bunny["mesh"].arrays()
+    r = ref.build_scene(pos, nrm, idx)
+    assert np.array_equal(util.raw(a["vertices"]), r["vertices"])
+    assert np.array_equal(util.raw(a["faces"]), r["faces"])
+    assert np.array_equal(util.raw(a["spheres"])[:, :20], r["spheres"][:, :20])
+    assert np.array_equal(util.raw(a["materials"])[:, :60], r["materials"][:, :60])
+    # Appendix A quirks 1/2: ids interleave smooth/flat, Cornell 0..11, floor last two
+    f = a["faces"]
+    assert len(f) == 138916 and (f["material"][:12:2] == np.arange(6)).all()
+    k = 12 + 2 * 1000
+    assert f["v2"][k + 1] == f["v0"][k + 1] + 1 and f["v1"][k + 1] == f["v0"][k + 1] + 2
+
+
+def test_bvh_topology_identical_to_reference_builder(rt, ref, bunny):
+    a = bunny["arrays"]
+    nodes, face_indices = ref.bvh_build(util.raw(a["vertices"]), util.raw(a["faces"]))
+    assert len(nodes) == 138545
+    assert np.array_equal(util.raw(a["nodes"]), nodes)
+    assert np.array_equal(a["face_indices"], face_indices)
+    leaves = a["nodes"][a["nodes"]["prim_count"] > 0]
+    assert len(leaves) == 69273 and leaves["prim_count"].max() == 345  # the fat leaf
+
+
+def test_small_scenes_bvh_vs_reference(rt, ref):
+    rng = np.random.default_rng(3)
+    for n in (1, 2, 3, 17, 200):
+        scene = rt.Scene()
+        m = scene.add_material()
+        for _ in range(n):
+            c = rng.uniform(-5, 5, 3)
+            tri = (c + rng.normal(size=(3, 3))).astype(np.float32)
+            scene.add_triangle(tri[0], tri[1], tri[2], m)
+        scene.build_bvh()
+        a = scene.arrays()
+        nodes, fi = ref.bvh_build(util.raw(a["vertices"]), util.raw(a["faces"]))
+        assert np.array_equal(util.raw(a["nodes"]), nodes) and np.array_equal(a["face_indices"], fi)
+
+
+def test_golden_hashes(rt, bunny):
+    """Runs everywhere (no /root/reference needed): arrays hash to what the GLM + BVH.cpp build produced."""
+    h = json.load(open(os.path.join(util.GOLDEN, "scene_hashes.json")))
+    a = bunny["arrays"]
+    assert sha(util.raw(a["vertices"])) == h["vertices"]
+    assert sha(util.raw(a["faces"])) == h["faces"]
+    assert sha(util.raw(a["nodes"])) == h["nodes"]
+    assert sha(a["face_indices"]) == h["face_indices"]
+    assert sha(util.raw(a["spheres"])[:, :20]) == h["spheres20"]
+    assert sha(util.raw(a["materials"])[:, :60]) == h["materials60"]
+    for name, (p, ax, ay) in util.POSES.items():
+        bunny["scene"].set_camera(p, ax, ay, 320, 240)
+        cam, _ = bunny["scene"].camera()
+        assert sha(cam.view(np.uint8)) == h["cameras"][name]
+
+
+def test_camera_vs_glm(rt, ref):
+    scene = rt.Scene()
+    for p, ax, ay, w, h in [((0, 0, 0), 0, 180, 640, 480), ((32, -1, 2), 0, 180, 1920, 1080), ((3, 4, -5), 17.5, -63.25, 3840, 2160)]:
+        scene.set_camera(p, ax, ay, w, h)
+        cam, _ = scene.camera()
+        assert np.array_equal(cam.view(np.uint8).ravel(), ref.camera(p, ax, ay, w, h))
+
+
+def test_dds_reader_roundtrip(rt):
+    tex = util.cubemap_texels()
+    out = np.zeros_like(tex)
+    size = rt.lib().rt_dds_read_level0(util.assets()["dds"].encode(), rt.ptr(out), out.size)
+    assert size == 128 and np.array_equal(out, tex)
+    assert rt.lib().rt_dds_read_level0(b"/nonexistent.dds", None, 0) == -4

@@ -1,0 +1,71 @@
+"""Shared helpers for tests / bench / smoke: asset materialisation from the committed fixtures, poses."""
+import os
+import struct
+import sys
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+if os.path.join(ROOT, "oracle") not in sys.path:
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+
+# SURVEY.md §8(d) config 1 poses: (position, angle_x, angle_y)
+POSES = {"default": ((0.0, 0.0, 0.0), 0.0, 180.0), "poseB": ((32.0, -1.0, 2.0), 0.0, 180.0)}
+
+_ASSET_DIR = None
+
+
+def write_obj(path, positions, indices):
+    with open(path, "w") as f:
+        f.write("# regenerated from tests/golden/bunny_mesh.npz (values round-trip float32 exactly)\n")
+        for p in positions:
+            f.write("v %.9g %.9g %.9g\n" % (p[0], p[1], p[2]))
+        for t in indices:
+            f.write("f %d %d %d\n" % (t[0] + 1, t[1] + 1, t[2] + 1))
+
+
+def write_dds_cubemap(path, texels):
+    """Legacy DDS, FourCC 116 (RGBA32F), six faces, one mip level - the layout of sunset_uncompressed.dds."""
+    size = texels.shape[1]
+    header = struct.pack("<7I", 124, 0x1 | 0x2 | 0x4 | 0x1000 | 0x20000, size, size, size * 16, 0, 1) + b"\0" * 44
+    header += struct.pack("<8I", 32, 0x4, 116, 0, 0, 0, 0, 0)
+    header += struct.pack("<5I", 0x1000 | 0x8 | 0x400000, 0xFE00, 0, 0, 0)
+    assert len(header) == 124
+    with open(path, "wb") as f:
+        f.write(b"DDS " + header + np.ascontiguousarray(texels, np.float32).tobytes())
+
+
+def assets():
+    """Paths of a temp OBJ + DDS rebuilt from the fixtures (the GPU box has no /root/reference)."""
+    global _ASSET_DIR
+    if _ASSET_DIR is None:
+        d = tempfile.mkdtemp(prefix="b200rt_assets_")
+        mesh = np.load(os.path.join(GOLDEN, "bunny_mesh.npz"))
+        write_obj(os.path.join(d, "stanford-bunny.obj"), mesh["positions"], mesh["indices"])
+        write_dds_cubemap(os.path.join(d, "sunset_uncompressed.dds"), np.load(os.path.join(GOLDEN, "sunset_level0.npz"))["texels"])
+        _ASSET_DIR = d
+    return {"obj": os.path.join(_ASSET_DIR, "stanford-bunny.obj"), "dds": os.path.join(_ASSET_DIR, "sunset_uncompressed.dds")}
+
+
+def cubemap_texels():
+    return np.ascontiguousarray(np.load(os.path.join(GOLDEN, "sunset_level0.npz"))["texels"], np.float32)
+
+
+def bunny_scene(rt, env=False):
+    """The reference's fixed scene (Cornell box + bunny + floor + emissive sphere), host side, BVH built."""
+    a = assets()
+    mesh = rt.Mesh(a["obj"])
+    scene = rt.Scene(a["dds"] if env else None)
+    scene.setup_cornell_box()
+    scene.setup_stanford_bunny(mesh)
+    scene.build_bvh()
+    return scene, mesh
+
+
+def raw(a):
+    """uint8 [n, itemsize] view of a structured array (what oracle/ref_oracle.py takes)."""
+    return np.ascontiguousarray(a).view(np.uint8).reshape(len(a), -1)

@@ -46,7 +46,7 @@ class ProcessParams(C.Structure):
                 ("max_bounces", C.c_int32), ("blend_mode", C.c_int32), ("variant", C.c_int32),
                 ("write_last_frame", C.c_int32), ("scene", C.c_void_p), ("accel", C.c_void_p),
                 ("d_ray_counter", C.c_void_p), ("stream", C.c_void_p), ("workspace", C.c_void_p),
-                ("workspace_bytes", C.c_uint64)]
+                ("workspace_bytes", C.c_uint64), ("d_work_counters", C.c_void_p)]
 
 
 class TracerOptions(C.Structure):
@@ -110,6 +110,7 @@ SYMBOLS = {
     "rt_host_tracer_destroy": (None, [_P]),
     "rt_host_tracer_process": (_I, [_P]),
     "rt_host_tracer_on_resize": (_I, [_P, _P, _P, _I, _I, _U64]),
+    "rt_host_tracer_render_to_host": (_I, [_P, _I, _P, _U64, C.POINTER(_U64)]),
     "rt_host_tracer_scene": (_P, [_P]),
     "rt_host_tracer_frame_index": (_I, [_P]),
     "rt_host_tracer_set_sampling": (_I, [_P, _I, _I, _I]),

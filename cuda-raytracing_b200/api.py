@@ -168,6 +168,12 @@ class Tracer:
     def process(self):
         check(lib().rt_host_tracer_process(self.handle))
 
+    def render_to_host(self, frames, host_pixels, host_pitch):
+        """Headless e2e call: `frames` progressive frames, surface copied into HOST memory. Returns h2d bytes moved."""
+        n = C.c_uint64()
+        check(lib().rt_host_tracer_render_to_host(self.handle, frames, ptr(host_pixels), host_pitch, C.byref(n)))
+        return n.value
+
     def on_resize(self, surface, last_frame_surface, width, height, pitch):
         self._keep = (surface, last_frame_surface)
         check(lib().rt_host_tracer_on_resize(self.handle, ptr(surface), ptr(last_frame_surface), width, height, pitch))
@@ -190,7 +196,7 @@ class Tracer:
 
 
 def process_ex(surface, last, width, height, pitch, frame_index, scene_ptr, accel_ptr, spp=5, bounces=6, blend_mode=0,
-               variant=0, write_last=0, ray_counter=None, stream=None):
+               variant=0, write_last=0, ray_counter=None, stream=None, work_counters=None):
     p = ProcessParams(ptr(surface), ptr(last), width, height, pitch, frame_index, spp, bounces, blend_mode, variant,
-                      write_last, scene_ptr, accel_ptr, ptr(ray_counter), ptr(stream), None, 0)
+                      write_last, scene_ptr, accel_ptr, ptr(ray_counter), ptr(stream), None, 0, ptr(work_counters))
     check(lib().rt_process_ex(C.byref(p)))

@@ -153,7 +153,7 @@ int rt_process_ex(const RtProcessParams* p)
     if (p->samples_per_launch <= 0 || p->max_bounces <= 0) return Fail(RT_E_INVALID, "rt_process_ex: spp and bounces must be positive");
     if (p->pitch < (uint64_t)p->width * 16) return Fail(RT_E_INVALID, "rt_process_ex: pitch smaller than a row");
     if (!p->scene->rng_state) return Fail(RT_E_INVALID, "rt_process_ex: scene has no rng_state");
-    if (p->variant != 0) return Fail(RT_E_INVALID, "rt_process_ex: unknown variant");
+    if (p->variant != 0 && p->variant != 2) return Fail(RT_E_INVALID, "rt_process_ex: unknown variant");
     RT_CUDA(LaunchPathTrace(p->accel->view, MakeSceneView(p->scene), *p, (cudaStream_t)p->stream));
     return RT_OK;
 }

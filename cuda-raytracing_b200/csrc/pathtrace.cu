@@ -27,6 +27,7 @@ struct FrameParams
     uint64_t pitch;
     int frame_index, spp, max_bounces, blend_mode, write_last;
     unsigned long long* ray_counter;
+    unsigned long long* work_counters;  // variant 2: [0] += nodes popped, [1] += triangle tests (reference traversal order)
     PathConsts consts;
 };
 
@@ -52,6 +53,9 @@ __device__ __forceinline__ void write_pixel(const FrameParams& P, int x, int y, 
     if (P.write_last) *(reinterpret_cast<float4*>(P.surface_last + (size_t)y * P.pitch) + x) = out;
 }
 
+// kMode 0: product traversal. kMode 2: reference-order traversal with work counters (measurement of the
+// algorithmic bytes per ray; same image up to exact-tie resolution).
+template <int kMode>
 __global__ void __launch_bounds__(256) pathtrace_megakernel(AccelView A, SceneView S, FrameParams P)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -59,6 +63,7 @@ __global__ void __launch_bounds__(256) pathtrace_megakernel(AccelView A, SceneVi
     const int y = blockIdx.y * 16 + (warp >> 1) * 4 + (lane >> 3);
     const bool active = x < P.width && y < P.height;
     unsigned rays = 0;
+    uint32_t work_nodes = 0, work_tris = 0;
     if (active)
     {
         RtRngState* state = S.rng_state + (size_t)y * P.width + x;  // GPUScene::GetRNGForPixel, GPUScene.h:95
@@ -80,7 +85,8 @@ __global__ void __launch_bounds__(256) pathtrace_megakernel(AccelView A, SceneVi
             const Vec3 nd = normalize3(ps.d);
             HitRecord h; h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
             sphere_tests(S.spheres, S.sphere_count, ps.o, nd, h);
-            trace_wide<false>(A, ps.o, ps.d, nd, h);
+            if (kMode == 0) trace_wide<false>(A, ps.o, ps.d, nd, h);
+            else trace_reference_order<false>(A, ps.o, ps.d, nd, h, &work_nodes, &work_tris);
             rays++;
             bool alive;
             if (h.id != RT_MISS_ID) alive = shade_hit(A, S, h, ps, rng) && (++bounce < P.max_bounces);
@@ -95,6 +101,11 @@ __global__ void __launch_bounds__(256) pathtrace_megakernel(AccelView A, SceneVi
         for (int o = 16; o; o >>= 1) rays += __shfl_xor_sync(0xffffffffu, rays, o);
         if (lane == 0 && rays) atomicAdd(P.ray_counter, (unsigned long long)rays);
     }
+    if (kMode == 2 && P.work_counters)
+    {
+        for (int o = 16; o; o >>= 1) { work_nodes += __shfl_xor_sync(0xffffffffu, work_nodes, o); work_tris += __shfl_xor_sync(0xffffffffu, work_tris, o); }
+        if (lane == 0) { atomicAdd(P.work_counters, (unsigned long long)work_nodes); atomicAdd(P.work_counters + 1, (unsigned long long)work_tris); }
+    }
 }
 
 cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, const RtProcessParams& p, cudaStream_t stream)
@@ -103,7 +114,7 @@ cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, cons
     P.surface = (unsigned char*)p.surface; P.surface_last = (unsigned char*)p.surface_last_frame;
     P.width = p.width; P.height = p.height; P.pitch = p.pitch; P.frame_index = p.frame_index;
     P.spp = p.samples_per_launch; P.max_bounces = p.max_bounces; P.blend_mode = p.blend_mode; P.write_last = p.write_last_frame;
-    P.ray_counter = p.d_ray_counter;
+    P.ray_counter = p.d_ray_counter; P.work_counters = p.d_work_counters;
     {   // glm quat(vec3(0, PI, 0)), type_quat.inl:204-213, in host fp32 like the oracle
         const float PI = 3.1415926536f;
         const float cx = std::cos(0.0f * 0.5f), cy = std::cos(PI * 0.5f), cz = std::cos(0.0f * 0.5f);
@@ -114,7 +125,8 @@ cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, cons
         P.consts.qz = cx * cy * sz - sx * sy * cz;
     }
     const dim3 grid((p.width + 15) / 16, (p.height + 15) / 16), block(256);
-    pathtrace_megakernel<<<grid, block, 0, stream>>>(accel, scene, P);
+    if (p.variant == 2) pathtrace_megakernel<2><<<grid, block, 0, stream>>>(accel, scene, P);
+    else pathtrace_megakernel<0><<<grid, block, 0, stream>>>(accel, scene, P);
     return cudaGetLastError();
 }
 

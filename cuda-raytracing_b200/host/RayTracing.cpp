@@ -66,6 +66,18 @@ namespace RayTracing
         frame_index++;                                                                          // :234
     }
 
+    size_t CUDARayTracer::RenderToHost(int frames, void* host_pixels, size_t host_pitch)
+    {
+        if (frames <= 0 || !host_pixels || host_pitch < (size_t)surface.width * 16) throw std::runtime_error("RenderToHost: bad argument");
+        size_t h2d = scene->RefreshDynamic();
+        scene->AddDirtyFlag(DirtyFlagValue::Samples);
+        for (int f = 0; f < frames; f++) { Process(); h2d += sizeof(RtGPUScene); }
+        const cudaError_t e = cudaMemcpy2D(host_pixels, host_pitch, surface.surface, surface.pitch, (size_t)surface.width * 16,
+                                           (size_t)surface.height, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) throw std::runtime_error(std::string("RenderToHost: ") + cudaGetErrorString(e));
+        return h2d;
+    }
+
     unsigned long long CUDARayTracer::GetRayCount() const
     {
         unsigned long long n = 0;

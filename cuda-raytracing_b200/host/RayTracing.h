@@ -38,6 +38,10 @@ namespace RayTracing
         void OnResize(SurfaceData surface);  // RayTracing.cpp:72-77
         Scene& GetScene() { return *scene; }
         void Process();                      // RayTracing.cpp:205-235
+        // Headless sink: restart accumulation, render `frames` Process() frames and copy the float4 surface into HOST
+        // memory (host_pitch bytes per row). Replaces the D3D11 present of main.cpp:683-716. Synchronous.
+        // Returns the host->device bytes this call moved (GPUScene by value per launch + refreshed spheres/materials).
+        size_t RenderToHost(int frames, void* host_pixels, size_t host_pitch);
         int GetFrameIndex() const { return frame_index; }
         Options& GetOptions() { return options; }
         unsigned long long GetRayCount() const;  // closest-hit queries since construction (device counter, synchronises)

@@ -79,6 +79,9 @@ namespace RayTracing
         void Upload(RtRngState* rng_state);  // device side; defined in SceneUpload.cpp (needs the CUDA library)
         void AddLoadedScene(const Loader::LoadedMesh& mesh, const mat4& transform = mat4(1.0f), int default_material = 0);
         void BuildBVH();                      // host part of Upload()'s BVH-dirty branch (Scene.cpp:189-191)
+        // Re-copies the per-frame mutable state (spheres, materials) into the existing device arrays; returns bytes copied.
+        // (The camera travels by value inside GPUScene, main_raytracing.cu:208-211.) Headless e2e path only.
+        size_t RefreshDynamic();
 
         Camera& GetCamera() { return camera; }
         void AddDirtyFlags(DirtyFlags flags = ~0u) { dirty_flags |= flags; }

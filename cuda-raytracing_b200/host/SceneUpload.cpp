@@ -81,4 +81,17 @@ namespace RayTracing
         }
         dirty_flags = 0;
     }
+
+    size_t Scene::RefreshDynamic()
+    {
+        if (!d_spheres || !d_materials || sphere_count != (int)spheres.size() || material_count != (int)materials.size())
+        {
+            AddDirtyFlag(DirtyFlagValue::SceneMemory);
+            return 0;
+        }
+        const size_t bs = spheres.size() * sizeof(RtSphere), bm = materials.size() * sizeof(RtMaterial);
+        if (bs) Check(cudaMemcpyAsync(d_spheres, spheres.data(), bs, cudaMemcpyHostToDevice, nullptr), "refresh spheres");
+        if (bm) Check(cudaMemcpyAsync(d_materials, static_cast<const RtMaterial*>(materials.data()), bm, cudaMemcpyHostToDevice, nullptr), "refresh materials");
+        return bs + bm;
+    }
 }

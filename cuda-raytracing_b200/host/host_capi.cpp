@@ -219,6 +219,13 @@ int rt_host_tracer_on_resize(RtHostTracer* t, void* surface, void* last, int wid
     return Guard([&] { t->tracer->OnResize(sd); return RT_OK; });
 }
 
+int rt_host_tracer_render_to_host(RtHostTracer* t, int frames, void* host_pixels, uint64_t host_pitch, uint64_t* h2d_bytes)
+{
+    if (!t) return rt_internal::Fail(RT_E_INVALID, "null tracer");
+    if (rt_device_count() <= 0) return rt_internal::Fail(RT_E_CUDA, "rt_host_tracer_render_to_host: no CUDA device (there is no CPU fallback)");
+    return Guard([&] { const size_t n = t->tracer->RenderToHost(frames, host_pixels, host_pitch); if (h2d_bytes) *h2d_bytes = n; return RT_OK; });
+}
+
 RtHostScene* rt_host_tracer_scene(RtHostTracer* t) { return t ? &t->scene_handle : nullptr; }
 int rt_host_tracer_frame_index(const RtHostTracer* t) { return t ? t->tracer->GetFrameIndex() : -1; }
 

@@ -66,6 +66,9 @@ int rt_host_tracer_create(void* surface, void* last_frame_surface, int width, in
 void rt_host_tracer_destroy(RtHostTracer* tracer);
 int rt_host_tracer_process(RtHostTracer* tracer);                 /* CUDARayTracer::Process */
 int rt_host_tracer_on_resize(RtHostTracer* tracer, void* surface, void* last_frame_surface, int width, int height, uint64_t pitch);
+/* Headless end-to-end call: restart accumulation, `frames` Process() frames, then the float4 surface -> HOST memory
+ * (replaces the D3D11 present, main.cpp:683-716). Synchronous. *h2d_bytes (optional) = host->device bytes moved. */
+int rt_host_tracer_render_to_host(RtHostTracer* tracer, int frames, void* host_pixels, uint64_t host_pitch, uint64_t* h2d_bytes);
 RtHostScene* rt_host_tracer_scene(RtHostTracer* tracer);          /* borrowed */
 int rt_host_tracer_frame_index(const RtHostTracer* tracer);
 int rt_host_tracer_set_sampling(RtHostTracer* tracer, int samples_per_launch, int max_bounces, int kernel_variant);

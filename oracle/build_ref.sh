@@ -21,6 +21,18 @@ sed 's/raytracing_kernel_main<<<Dg, Db>>>(render_data);/(void)Dg; (void)render_d
     "$R/RayTracing/main_raytracing.cu" > "$OUT/rt_host.inc"
 g++ $CXXFLAGS $INC -I"$R/RayTracing" -DRT_HOST_SRC="\"$OUT/rt_host.inc\"" \
     -c "$HERE/ref_shim/ref_api.cpp" -o "$OUT/ref_api.o"
-g++ -shared -fopenmp -o "$OUT/libref_oracle.so" "$OUT/ref_api.o" "$OUT/bvh_ref.o"
-rm -f "$OUT/rt_host.inc" "$OUT"/*.o
+# CPU-baseline variant (bench.py only): constants -> variables, GetRayHit counter, -O3 -march=native is NOT used
+# (the .so is built in the container and must run on the GPU box's host CPU): -O3 only.
+sed -e 's/raytracing_kernel_main<<<Dg, Db>>>(render_data);/(void)Dg; (void)render_data;/' \
+    -e 's/constexpr int num_bounces = 6;/const int num_bounces = refbench_bounces;/' \
+    -e 's/constexpr int sample_count = 5;/const int sample_count = refbench_spp;/' \
+    -e 's/result.distance = max_distance;/result.distance = max_distance; refbench_rays++;/' \
+    -e 's/extern "C" void raytracing_process/extern "C" void refbench_raytracing_process/' \
+    -e 's/^#include "Math.h"//' -e 's/^#include "GPUScene.h"//' \
+    "$R/RayTracing/main_raytracing.cu" > "$OUT/rt_bench.inc"
+grep -q refbench_bounces "$OUT/rt_bench.inc" && grep -q refbench_spp "$OUT/rt_bench.inc" && grep -q 'refbench_rays++' "$OUT/rt_bench.inc"
+g++ ${CXXFLAGS/-O2/-O3} $INC -I"$R/RayTracing" -DRT_BENCH_SRC="\"$OUT/rt_bench.inc\"" \
+    -c "$HERE/ref_shim/ref_bench.cpp" -o "$OUT/ref_bench.o"
+g++ -shared -fopenmp -o "$OUT/libref_oracle.so" "$OUT/ref_api.o" "$OUT/ref_bench.o" "$OUT/bvh_ref.o"
+rm -f "$OUT/rt_host.inc" "$OUT/rt_bench.inc" "$OUT"/*.o
 echo "built $OUT/libref_oracle.so"

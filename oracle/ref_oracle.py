@@ -120,3 +120,22 @@ def render_frame(scene, nodes, face_indices, cam60, cubemap, rng_states, surface
                            len(scene["spheres"]), _p(scene["materials"]), len(scene["materials"]), _p(cam60),
                            _p(cubemap), 0 if cubemap is None else cubemap.shape[1], _p(rng_states), _p(surface), _p(last),
                            width, height, width * 16, frame_index, row_begin, row_end)
+
+
+def bench_render(scene, nodes, face_indices, cam60, cubemap, rng_states, surface, last, width, height, frame_index,
+                 row_begin, row_stride, spp, bounces):
+    """CPU baseline: the reference kernel body (constants made runtime, ref_shim/ref_bench.cpp) over every
+    `row_stride`-th row with all host threads. Returns (seconds, rays = GetRayHit calls, threads)."""
+    h = lib()
+    h.ref_bench_render.restype = C.c_double
+    h.ref_bench_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
+                                   C.c_uint32, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                   C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                   C.c_void_p, C.c_void_p]
+    rays = C.c_ulonglong(); threads = C.c_int()
+    s = h.ref_bench_render(_p(scene["vertices"]), _p(scene["faces"]), _p(nodes), _p(face_indices), _p(scene["spheres"]),
+                           len(scene["spheres"]), _p(scene["materials"]), len(scene["materials"]), _p(cam60),
+                           _p(cubemap), 0 if cubemap is None else cubemap.shape[1], _p(rng_states), _p(surface), _p(last),
+                           width, height, width * 16, frame_index, row_begin, row_stride, spp, bounces,
+                           C.addressof(rays), C.addressof(threads))
+    return s, rays.value, threads.value

@@ -12,6 +12,8 @@ Outputs (tests/golden/):
                       with and without spheres
   rng_kat.npz         curand_init(seed, subsequence, 0) + curand() known answers from the toolkit's header
   rays_kat.npz        4096 seeded incoherent rays through GetRayHit (ids, t)
+  pt_96x72.npz        raytracing_kernel_main run per pixel on the host (5 spp x 6 bounces, seed 1234, pose B,
+                      sunset env map through oracle/cubemap_cpu.h): surfaces after frames 0,1,2 + final RNG states
 """
 import hashlib
 import json
@@ -112,6 +114,13 @@ def main():
     ro.lib().ref_rng_draw_uniform(st[2].ctypes.data, 16, uni.ctypes.data)
     kat["uniform_seed1234_sub2"] = uni
     np.savez_compressed(os.path.join(HERE, "rng_kat.npz"), **kat)
+    # path-traced frames (full kernel body incl. accumulation), small enough to commit
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import gpu_util
+    import util
+    uscene, _ = util.bunny_scene(rt)
+    frames, states = gpu_util.oracle_frames(ro, rt, uscene, 96, 72, "poseB", 1234, 3, np.ascontiguousarray(texels, np.float32))
+    np.savez_compressed(os.path.join(HERE, "pt_96x72.npz"), frames=np.stack(frames), rng_v=states[:96 * 72, :24].copy())
     for f in sorted(os.listdir(HERE)):
         print(f, os.path.getsize(os.path.join(HERE, f)))
 

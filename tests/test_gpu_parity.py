@@ -1,0 +1,272 @@
+"""-m gpu parity tests: the sm_100a kernels, called through the C ABI (include/b200rt.h), against
+  * the committed golden vectors produced by the reference's own code compiled host-side
+    (tests/golden/make_fixtures.py, oracle/_ref), and
+  * oracle/_ref itself on fresh seeded inputs when the prebuilt library travelled to the box.
+Bars (BASELINE.json north_star): primary closest-hit ids bit-exact (exact ties -> lowest id), t within 1e-5 relative
+(observed: bit-exact), RNG stream bit-exact, path-traced images by RMSE (the hardware cubemap filter and device
+sin/cos differ from the host restatement in the last ulps)."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+import gpu_util
+import util
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev(rt, torch_cuda):
+    return gpu_util.DeviceScene(rt, torch_cuda, 320, 240, "default", seed=1234)
+
+
+def golden(name):
+    return np.load(os.path.join(util.GOLDEN, name))
+
+
+def check_ids(ids, ts, gid, gt, allow_tie_swaps=True):
+    """ids/t against the reference's first-visited result. t must agree bit for bit; ids may differ only on exact
+    t-ties between the smooth/flat duplicate of the same bunny face, where the product
+    rule picks the LOWER id (BASELINE.json) and the reference the first visited."""
+    assert np.array_equal(ts.view(np.uint32), gt.view(np.uint32)), "t differs: %d rays" % int((ts.view(np.uint32) != gt.view(np.uint32)).sum())
+    bad = np.nonzero(ids != gid)[0]
+    if len(bad) == 0:
+        return 0
+    assert allow_tie_swaps
+    a, b = ids[bad].astype(np.int64), gid[bad].astype(np.int64)
+    assert ((a >= 12) & (b >= 12) & ((a - 12) // 2 == (b - 12) // 2) & (a < b)).all(), "id mismatch that is not a duplicate-face tie"
+    return len(bad)
+
+
+# ------------------------------------------------------------------ RNG
+def test_rng_known_answers_bit_exact(rt, torch_cuda):
+    t = torch_cuda
+    g = golden("rng_kat.npz")
+    for i, seed in enumerate(g["seeds"]):
+        for j, sub in enumerate(g["subsequences"]):
+            st = t.zeros(48, dtype=t.uint8, device="cuda")
+            out = t.zeros(8, dtype=t.int32, device="cuda")
+            rt.check(rt.lib().rt_init_rng(rt.ptr(st), 1, int(seed), int(sub), None))
+            rt.check(rt.lib().rt_rng_draw(rt.ptr(st), 1, 8, rt.ptr(out), None))
+            assert np.array_equal(out.cpu().numpy().view(np.uint32), g["draws"][i, j]), (seed, sub)
+
+
+def test_rng_init_matches_curand_init_for_every_pixel_stream(rt, torch_cuda, ref):
+    """init_rng (the reference-named entry) over a whole padded frame == host curand_init for each subsequence."""
+    t = torch_cuda
+    n = gpu_util.rng_state_count(320, 240)
+    st = t.zeros(n * 48, dtype=t.uint8, device="cuda")
+    rt.lib().init_rng(n // 128, 128, rt.ptr(st), 0xDEADBEEF)
+    t.cuda.synchronize()
+    mine = st.cpu().numpy().reshape(n, 48)
+    want = ref.rng_init(n, 0xDEADBEEF)
+    assert np.array_equal(mine[:, :24], want[:, :24])  # d, v[5]
+    assert not mine[:, 24:36].any()                    # Box-Muller flags/extra zeroed like curand_init
+
+
+def test_rng_uniform_and_state_roundtrip(rt, torch_cuda):
+    t = torch_cuda
+    g = golden("rng_kat.npz")
+    st = t.zeros(48 * 4, dtype=t.uint8, device="cuda")
+    rt.check(rt.lib().rt_init_rng(rt.ptr(st), 4, 1234, 0, None))
+    a = t.zeros(4 * 16, dtype=t.int32, device="cuda")
+    # two draws of 8 == one draw of 16 (state persists in the 48-B curandState between launches)
+    b = t.zeros(4 * 8, dtype=t.int32, device="cuda"); c = t.zeros(4 * 8, dtype=t.int32, device="cuda")
+    st2 = st.clone()
+    rt.check(rt.lib().rt_rng_draw(rt.ptr(st), 4, 16, rt.ptr(a), None))
+    rt.check(rt.lib().rt_rng_draw(rt.ptr(st2), 4, 8, rt.ptr(b), None))
+    rt.check(rt.lib().rt_rng_draw(rt.ptr(st2), 4, 8, rt.ptr(c), None))
+    a = a.cpu().numpy().view(np.uint32).reshape(4, 16)
+    assert np.array_equal(a[:, :8], b.cpu().numpy().view(np.uint32).reshape(4, 8))
+    assert np.array_equal(a[:, 8:], c.cpu().numpy().view(np.uint32).reshape(4, 8))
+    # curand_uniform = x * 2^-32 + 2^-33 (curand_uniform.h:69-72)
+    uni = (a[2].astype(np.float32) * np.float32(2.3283064e-10) + np.float32(2.3283064e-10 / 2)).astype(np.float32)
+    assert np.array_equal(uni, g["uniform_seed1234_sub2"])
+
+
+# ------------------------------------------------------------------ closest hit
+@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("pose", ["default", "poseB"])
+@pytest.mark.parametrize("with_spheres", [0, 1])
+def test_primary_hits_vs_reference_golden(dev, pose, with_spheres, variant):
+    g = golden("primary_320x240.npz")
+    dev.set_pose(pose)
+    ids, ts = dev.trace_primary(with_spheres, variant)
+    swaps = check_ids(ids, ts, g[f"{pose}_s{with_spheres}_id"], g[f"{pose}_s{with_spheres}_t"])
+    assert swaps <= 64, swaps
+    hit = ids != 0xFFFFFFFF
+    assert 0.3 < hit.mean() <= 1.0
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+def test_incoherent_rays_vs_reference_golden(dev, variant):
+    g = golden("rays_kat.npz")
+    ids, ts = dev.trace_rays(g["rays"], True, variant)
+    check_ids(ids, ts, g["ids"], g["t"])
+
+
+def test_fresh_random_rays_vs_live_oracle(dev, ref):
+    """Seeded rays that are NOT in the fixtures, through oracle/_ref's unmodified GetRayHit on the box's host."""
+    rng = np.random.default_rng(20261104)
+    n = 20000
+    o = rng.uniform([15, -12, 5], [45, 12, 35], (n, 3)).astype(np.float32)
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    rays = np.concatenate([o, d], 1)
+    # axis-aligned directions (zero components: division by zero in the slab test, Math.h:50-61)
+    rays[:64, 3:] = 0; rays[:64, 3 + (np.arange(64) % 3)] = np.where(np.arange(64) % 2, 1.0, -1.0)
+    a = dev.scene.arrays()
+    gid, gt = ref.trace_rays(util.raw(a["vertices"]), util.raw(a["faces"]), util.raw(a["nodes"]), a["face_indices"],
+                             util.raw(a["spheres"]), rays, True)
+    for variant in (0, 1):
+        ids, ts = dev.trace_rays(rays, True, variant)
+        check_ids(ids, ts, gid, gt)
+
+
+def test_product_kernel_equals_reference_order_kernel_at_1080p(rt, torch_cuda):
+    """Size-independent property at BASELINE's full resolution: the near-first wide traversal returns exactly what
+    the reference-order traversal returns (ids and t bit for bit), both poses."""
+    d = gpu_util.DeviceScene(rt, torch_cuda, 1920, 1080, "poseB", env=False)
+    for pose in ("poseB", "default"):
+        d.set_pose(pose)
+        i0, t0 = d.trace_primary(1, 0)
+        i1, t1 = d.trace_primary(1, 1)
+        assert np.array_equal(i0, i1) and np.array_equal(t0.view(np.uint32), t1.view(np.uint32))
+    assert d.rays() == 4 * 1920 * 1080
+
+
+def test_edge_cases(rt, torch_cuda):
+    t = torch_cuda
+    # one-triangle scene, no spheres, width/height not multiples of the 16x16 tile
+    scene = rt.Scene()
+    scene.add_triangle((-1, -1, 3), (1, -1, 3), (0, 1, 3), scene.add_material(albedo=(0.5, 0.5, 0.5)))
+    scene.build_bvh()
+    d = gpu_util.DeviceScene(rt, t, 37, 23, ((0, 0, 0), 0.0, 180.0), env=False, scene=scene)
+    for variant in (0, 1):
+        ids, ts = d.trace_primary(0, variant)
+        assert set(np.unique(ids)) == {0, 0xFFFFFFFF}
+        assert (ts[ids == 0] >= 3).all() and (ts[ids == 0] < 6).all() and (ts[ids == 0xFFFFFFFF] == np.float32(1e30)).all()
+    # zero rays is a no-op, not an error
+    ids, ts = d.trace_rays(np.zeros((0, 6), np.float32), False, 0)
+    assert len(ids) == 0
+    # argument errors come back as codes, never exits (utils/CUDAHelper.h:7-22 exits; this layer must not)
+    assert rt.lib().rt_trace_primary(None, d.gpu, 4, 4, 0, 0, None, None, None, None) == -1
+    assert rt.lib().rt_trace_primary(d.accel, d.gpu, 4, 4, 0, 7, rt.ptr(d.counter), rt.ptr(d.counter), None, None) == -1
+    assert rt.lib().rt_process_ex(None) == -1
+    assert b"bad argument" in rt.lib().rt_last_error()
+    # a path-traced frame of the one-triangle scene: finite, alpha 1
+    d.process(0)
+    s = d.surface.cpu().numpy()
+    assert np.isfinite(s).all() and (s[..., 3] == 1).all()
+
+
+# ------------------------------------------------------------------ path tracing
+def rel_rmse(a, b):
+    return float(np.sqrt(np.mean((a[..., :3] - b[..., :3]) ** 2)) / max(np.sqrt(np.mean(b[..., :3] ** 2)), 1e-12))
+
+
+def test_path_trace_frames_vs_reference_golden(rt, torch_cuda):
+    """Same seed, same per-pixel stream, same fp32 expression order => the frames track the host-run reference kernel
+    body pixel by pixel. Residual differences: device sinf/cosf vs glibc, hardware cubemap filter vs cubemap_cpu.h."""
+    g = golden("pt_96x72.npz")
+    d = gpu_util.DeviceScene(rt, torch_cuda, 96, 72, "poseB", seed=1234, env=True)
+    for f in range(3):
+        d.process(f, write_last=1)
+        got = d.surface.cpu().numpy()
+        want = g["frames"][f]
+        assert (got[..., 3] == 1).all()
+        close = np.isclose(got[..., :3], want[..., :3], rtol=2e-2, atol=2e-3).all(axis=-1)
+        assert close.mean() > 0.97, (f, close.mean())
+        assert rel_rmse(got, want) < 0.05, (f, rel_rmse(got, want))
+        assert np.array_equal(d.last.cpu().numpy(), got)  # folded D2D copy (RayTracing.cpp:233)
+    # the per-pixel XORWOW streams advanced by the same number of draws as the reference's (path lengths equal)
+    st = d.rng.cpu().numpy().reshape(-1, 48)[: 96 * 72, :24]
+    same = (st == g["rng_v"]).all(axis=1).mean()
+    assert same > 0.97, same
+
+
+def test_reference_named_entry_and_accumulation_semantics(rt, torch_cuda):
+    t = torch_cuda
+    d = gpu_util.DeviceScene(rt, t, 64, 48, "poseB", seed=7, env=True)
+    # raytracing_process (main_raytracing.cu:202): 5 spp, 6 bounces, lerp(last, mean, 1/(frame+1)), alpha = 1
+    rt.lib().raytracing_process(rt.ptr(d.surface), rt.ptr(d.last), 64, 48, d.pitch, 0, d.gpu)
+    t.cuda.synchronize()
+    f0 = d.surface.clone()
+    assert (f0[..., 3] == 1).all() and t.isfinite(f0).all()
+    assert (d.last == 0).all()  # the reference-named entry leaves the last-frame copy to its caller (RayTracing.cpp:233)
+    d2 = gpu_util.DeviceScene(rt, t, 64, 48, "poseB", seed=7, env=True)
+    d2.process(0, spp=5, bounces=6)
+    assert t.equal(d2.surface, f0)  # same seed -> bit-identical frame through either entry
+    # frame 1 = lerp(frame0, estimate1, 1/2): run the same estimate into an empty buffer and blend on the host
+    d.last.copy_(d.surface)
+    rng_before = d.rng.clone()
+    rt.lib().raytracing_process(rt.ptr(d.surface), rt.ptr(d.last), 64, 48, d.pitch, 1, d.gpu)
+    t.cuda.synchronize()
+    d.rng.copy_(rng_before)
+    est = t.zeros_like(d.surface)
+    d.process(0, surface=est, last=t.zeros_like(est))
+    a = np.float32(0.5)
+    want = f0.cpu().numpy() * (np.float32(1) - a) + est.cpu().numpy() * a
+    want[..., 3] = 1
+    assert np.array_equal(d.surface.cpu().numpy(), want)
+    # blend_mode 1: sum buffer (+ sample count in alpha) for the multi-GPU split
+    d.rng.copy_(rng_before)
+    acc = t.zeros_like(d.surface)
+    d.process(0, blend_mode=1, surface=acc, last=None)
+    got = acc.cpu().numpy()
+    assert (got[..., 3] == 5).all()
+    assert np.allclose(got[..., :3] / 5, est.cpu().numpy()[..., :3], rtol=1e-6, atol=1e-7)
+
+
+def test_sample_split_is_stream_continuous(rt, torch_cuda):
+    """One launch of 10 spp == two launches of 5 spp (sum buffers): the per-pixel stream is continuous across launches."""
+    t = torch_cuda
+    a = gpu_util.DeviceScene(rt, t, 64, 48, "poseB", seed=99, env=True)
+    b = gpu_util.DeviceScene(rt, t, 64, 48, "poseB", seed=99, env=True)
+    sa = t.zeros_like(a.surface); sb = t.zeros_like(a.surface)
+    a.process(0, spp=10, bounces=4, blend_mode=1, surface=sa)
+    b.process(0, spp=5, bounces=4, blend_mode=1, surface=sb)
+    b.process(1, spp=5, bounces=4, blend_mode=1, surface=sb)
+    assert t.equal(a.rng, b.rng)
+    assert t.allclose(sa, sb, rtol=1e-5, atol=1e-6)
+    assert a.rays() == b.rays() > 64 * 48 * 10
+
+
+def test_tracer_facade_process_and_resize(rt, torch_cuda):
+    """CUDARayTracer mirror (RayTracing.h:12-45): Process() advances frame_index, OnResize restarts accumulation."""
+    t = torch_cuda
+    a = util.assets()
+    s = t.zeros((48, 64, 4), dtype=t.float32, device="cuda"); l = t.zeros_like(s)
+    tr = rt.Tracer(s, l, 64, 48, 64 * 16, bunny_obj=a["obj"], env_dds=a["dds"], seed=5)
+    tr.scene.set_camera(*util.POSES["poseB"], 64, 48)
+    tr.process(); tr.process()
+    t.cuda.synchronize()
+    assert tr.frame_index == 2 and t.equal(s, l) and (s[..., 3] == 1).all()
+    assert tr.ray_count > 2 * 5 * 64 * 48
+    s2 = t.zeros((24, 32, 4), dtype=t.float32, device="cuda"); l2 = t.zeros_like(s2)
+    tr.on_resize(s2, l2, 32, 24, 32 * 16)
+    tr.process()
+    t.cuda.synchronize()
+    assert tr.frame_index == 1 and (s2[..., 3] == 1).all() and float(s2[..., :3].mean()) > 0
+
+
+def test_ambient_occlusion_and_tonemap(rt, torch_cuda):
+    t = torch_cuda
+    d = gpu_util.DeviceScene(rt, t, 160, 120, "poseB", seed=3, env=False)
+    ao = t.zeros(160 * 120, dtype=t.float32, device="cuda")
+    rt.check(rt.lib().rt_ambient_occlusion(d.accel, d.gpu, 160, 120, 16, rt.ptr(ao), rt.ptr(d.counter), None))
+    v = ao.cpu().numpy()
+    assert ((v >= 0) & (v <= 1)).all() and 0.05 < v.mean() < 0.99
+    ids, _ = d.trace_primary(1, 0)
+    hits = int((ids != 0xFFFFFFFF).sum())
+    assert d.rays() == 160 * 120 + 16 * hits + 160 * 120  # AO: 1 primary/pixel + 16 per hit; then the id query
+    # tonemap: exposure 0.5 + ACES + sRGB + vertical flip (main.cpp:65-94), against numpy
+    surf = t.rand((120, 160, 4), dtype=t.float32, device="cuda") * 4
+    out = t.zeros((120, 160, 4), dtype=t.uint8, device="cuda")
+    rt.check(rt.lib().rt_tonemap_rgba8(rt.ptr(surf), 160, 120, 160 * 16, 1.0, rt.ptr(out), None))
+    x = surf.cpu().numpy()[..., :3].astype(np.float64) * 0.5
+    y = np.clip((x * (2.51 * x + 0.03)) / (x * (2.43 * x + 0.59) + 0.14), 0, 1)
+    y = np.where(y <= 0.0031308, 12.92 * y, 1.055 * y ** (1 / 2.4) - 0.055)
+    want = np.floor(y * 255 + 0.5)[::-1]
+    assert np.abs(out.cpu().numpy()[..., :3].astype(np.float64) - want).max() <= 1

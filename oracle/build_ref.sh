@@ -3,7 +3,7 @@
 # LIE under /root/reference (nothing is copied into the repo; outputs only into oracle/_ref/, which
 # is git-ignored but travels to the GPU box). Recipe follows SURVEY.md Appendix B:
 #   - RayTracing/BVH.cpp compiled verbatim (Linux pch stand-in, two empty Assimp stubs, a case shim)
-#   - RayTracing/main_raytracing.cu compiled as host C++ after ONE mechanical edit (the <<<>>> launch)
+#   - RayTracing/main_raytracing.cu compiled as host C++ after TWO mechanical edits (the <<<>>> launch; the jitter draw order)
 #   - cuRAND XORWOW from the toolkit's own header, host-side
 # The reference's own build system (MSBuild/vcpkg) is not run.
 set -euo pipefail
@@ -17,13 +17,16 @@ INC="-I$R -I$R/include -I$R/Common -I$CUDA_INC -DGLM_ENABLE_EXPERIMENTAL -I$HERE
 # -ffp-contract=off: the oracle's arithmetic is plain IEEE mul/add (no FMA) - DESIGN.md "contraction policy"
 CXXFLAGS="-std=c++20 -O2 -w -fPIC -fopenmp -ffp-contract=off"
 g++ $CXXFLAGS $INC -include "$HERE/ref_shim/pch_linux.h" -c "$R/RayTracing/BVH.cpp" -o "$OUT/bvh_ref.o"
-sed 's/raytracing_kernel_main<<<Dg, Db>>>(render_data);/(void)Dg; (void)render_data;/' \
+# Edit 2 pins an evaluation order C++ leaves unspecified to the one nvcc emits for the device (x jitter drawn first).
+JITTER='s/vec2(rng.GetFloat01(), rng.GetFloat01())/ref_jitter_device_order<vec2>(rng)/'
+sed -e 's/raytracing_kernel_main<<<Dg, Db>>>(render_data);/(void)Dg; (void)render_data;/' -e "$JITTER" \
     "$R/RayTracing/main_raytracing.cu" > "$OUT/rt_host.inc"
+grep -q 'ref_jitter_device_order<vec2>(rng)' "$OUT/rt_host.inc"
 g++ $CXXFLAGS $INC -I"$R/RayTracing" -DRT_HOST_SRC="\"$OUT/rt_host.inc\"" \
     -c "$HERE/ref_shim/ref_api.cpp" -o "$OUT/ref_api.o"
 # CPU-baseline variant (bench.py only): constants -> variables, GetRayHit counter, -O3 -march=native is NOT used
 # (the .so is built in the container and must run on the GPU box's host CPU): -O3 only.
-sed -e 's/raytracing_kernel_main<<<Dg, Db>>>(render_data);/(void)Dg; (void)render_data;/' \
+sed -e 's/raytracing_kernel_main<<<Dg, Db>>>(render_data);/(void)Dg; (void)render_data;/' -e "$JITTER" \
     -e 's/constexpr int num_bounces = 6;/const int num_bounces = refbench_bounces;/' \
     -e 's/constexpr int sample_count = 5;/const int sample_count = refbench_spp;/' \
     -e 's/result.distance = max_distance;/result.distance = max_distance; refbench_rays++;/' \

@@ -41,3 +41,13 @@ template <> inline float4 texCubemapLod<float4>(cudaTextureObject_t tex, float x
     const OracleFloat4 v = oracle_tex_cubemap_lod0(*cm, x, y, z);
     return make_float4(v.x, v.y, v.z, v.w);
 }
+
+// C++ leaves the evaluation order of `vec2(rng.GetFloat01(), rng.GetFloat01())` (main_raytracing.cu:190) unspecified.
+// nvcc's device code draws the x jitter first (PTX evidence: DESIGN.md "jitter order"); g++ would draw y first. The host
+// build pins the device order through this helper (build_ref.sh substitutes the one expression).
+template <class V, class R> static inline V ref_jitter_device_order(R& rng)
+{
+    const float jx = rng.GetFloat01();
+    const float jy = rng.GetFloat01();
+    return V(jx, jy);
+}

@@ -10,6 +10,8 @@ Outputs (tests/golden/):
   scene_hashes.json   sha256 of the reference-layout arrays + BVH the GLM/BVH.cpp build produces
   primary_320x240.npz reference BVHRayHit/GetRayHit closest-hit ids (first-visited rule) + t, two poses,
                       with and without spheres
+  primary_320x240_lowest_id.npz  the same queries under the order-independent rule (min t, ties -> lowest id), from
+                      oracle/rt_port.c after its reference-rule mode is asserted equal to the reference's output
   rng_kat.npz         curand_init(seed, subsequence, 0) + curand() known answers from the toolkit's header
   rays_kat.npz        4096 seeded incoherent rays through GetRayHit (ids, t)
   pt_96x72.npz        raytracing_kernel_main run per pixel on the host (5 spp x 6 bounces, seed 1234, pose B,
@@ -114,6 +116,26 @@ def main():
     ro.lib().ref_rng_draw_uniform(st[2].ctypes.data, 16, uni.ctypes.data)
     kat["uniform_seed1234_sub2"] = uni
     np.savez_compressed(os.path.join(HERE, "rng_kat.npz"), **kat)
+    # ids under the ORDER-INDEPENDENT rule the product implements (min t, exact ties -> lowest id; BASELINE.json):
+    # produced by the plain-C port (oracle/rt_port.c, tie_mode 1) AFTER asserting that its tie_mode 0 reproduces the
+    # unmodified reference functions bit for bit on the same rays.
+    import port_oracle as po
+    ps = po.PortScene(scene, nodes, face_indices, None, None)
+    low = {}
+    for name, (p, ax, ay) in POSES.items():
+        ps.set(ro.camera(p, ax, ay, 320, 240))
+        for ws in (0, 1):
+            i0, t0 = ps.primary_hits(320, 240, ws, 0)
+            assert np.array_equal(i0, out[f"{name}_s{ws}_id"]) and np.array_equal(t0.view(np.uint32), out[f"{name}_s{ws}_t"].view(np.uint32))
+            i1, t1 = ps.primary_hits(320, 240, ws, 1)
+            assert np.array_equal(t1.view(np.uint32), t0.view(np.uint32)) and (i1 <= i0).all()
+            low[f"{name}_s{ws}_id"] = i1
+            print(name, ws, "tie swaps:", int((i1 != i0).sum()))
+    i0, t0 = ps.trace_rays(rays, True, 0)
+    assert np.array_equal(i0, ids) and np.array_equal(t0.view(np.uint32), ts.view(np.uint32))
+    low["rays_id"], _ = ps.trace_rays(rays, True, 1)
+    np.savez_compressed(os.path.join(HERE, "primary_320x240_lowest_id.npz"), **low)
+
     # path-traced frames (full kernel body incl. accumulation), small enough to commit
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import gpu_util

@@ -92,7 +92,7 @@ __device__ __forceinline__ void closest_hit(const AccelView& A, const SceneView&
     const Vec3 nd = normalize3(d);
     h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
     if (with_spheres) sphere_tests(S.spheres, S.sphere_count, o, nd, h);
-    if (kVariant == 0) trace_wide<true>(A, o, d, nd, h);
+    if (kVariant == 0 && dot3(d, d) >= RT_SHORT_DIR2) trace_wide<true>(A, o, d, nd, h);
     else trace_reference_order<true>(A, o, d, nd, h);
 }
 

@@ -41,6 +41,9 @@ __device__ __forceinline__ float4 ldg4(const void* p) { return __ldg(reinterpret
 
 // Math::IntersectAABB with the reference's operand roles. Order-independent use: ray_length = the
 // distance the BVH search STARTED with (sphere hit or 1e30).
+// kInclusive: `tmin <= ray_length` instead of the reference's `<` - used only by the lowest-id tie rule, where a node whose
+// entry distance EQUALS the current best can still hold an exact-tie candidate with a lower id.
+template <bool kInclusive = false>
 __device__ __forceinline__ bool exact_box(Vec3 o, Vec3 d, const RtBVHNode* node, float ray_length)
 {
     const float4 q0 = ldg4(node);                                    // min.xyz max.x
@@ -51,8 +54,14 @@ __device__ __forceinline__ bool exact_box(Vec3 o, Vec3 d, const RtBVHNode* node,
     tmin = fmaxf(tmin, fminf(ty1, ty2)); tmax = fminf(tmax, fmaxf(ty1, ty2));
     const float tz1 = (q0.z - o.z) / d.z, tz2 = (q1.y - o.z) / d.z;
     tmin = fmaxf(tmin, fminf(tz1, tz2)); tmax = fminf(tmax, fmaxf(tz1, tz2));
-    return tmax >= tmin && tmin < ray_length && tmax > 0;
+    return tmax >= tmin && (kInclusive ? tmin <= ray_length : tmin < ray_length) && tmax > 0;
 }
+
+// Rays shorter than unit length (|d|^2 below this) make the reference's box cull NON-conservative (Math.h:50-61 compares an
+// unnormalised-units entry distance with a normalised-units best, Appendix A.4): its result then depends on its own visiting
+// order, so such rays take the reference-order traversal in every variant. Camera rays have |d| >= 1 and bounce rays are
+// normalised, so the path tracer never takes this branch; it exists for rt_trace_rays' "direction as given" contract.
+#define RT_SHORT_DIR2 0.99999f
 
 // glm::intersectRayTriangle on a TriRecord. Returns true with (t, bu, bv) when GLM would.
 __device__ __forceinline__ bool tri_test(Vec3 o, Vec3 nd, float4 r0, float4 r1, float4 r2, float& t, float& bu, float& bv)
@@ -181,11 +190,12 @@ __device__ __forceinline__ void trace_reference_order(const AccelView& A, Vec3 o
     uint32_t stack[RT_STACK_SIZE];
     int sp = 0;
     stack[sp++] = 0;
+    const bool inclusive = kTieById && dot3(d, d) >= RT_SHORT_DIR2;
     while (sp)
     {
         const RtBVHNode* n = A.ref_nodes + stack[--sp];
         if (nodes_popped) (*nodes_popped)++;
-        if (!exact_box(o, d, n, h.t)) continue;
+        if (!(inclusive ? exact_box<true>(o, d, n, h.t) : exact_box<false>(o, d, n, h.t))) continue;
         const float4 q1 = ldg4(reinterpret_cast<const char*>(n) + 16);
         const uint32_t first = __float_as_uint(q1.z), count = __float_as_uint(q1.w);
         if (count)

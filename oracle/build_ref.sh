@@ -39,3 +39,13 @@ g++ ${CXXFLAGS/-O2/-O3} $INC -I"$R/RayTracing" -DRT_BENCH_SRC="\"$OUT/rt_bench.i
 g++ -shared -fopenmp -o "$OUT/libref_oracle.so" "$OUT/ref_api.o" "$OUT/ref_bench.o" "$OUT/bvh_ref.o"
 rm -f "$OUT/rt_host.inc" "$OUT/rt_bench.inc" "$OUT"/*.o
 echo "built $OUT/libref_oracle.so"
+# The reference's own CUDA kernels, UNMODIFIED, for sm_100a (BASELINE.json: "where the reference's own CUDA kernel builds
+# for sm_100, its numbers are reported alongside"). Default nvcc flags as in RayTracing.vcxproj (no fast-math, fmad on).
+# Exports the reference's extern "C" raytracing_process / init_rng; driven headless by tests/bench through ctypes.
+NVCC="${CUDA_HOME:-/usr/local/cuda}/bin/nvcc"
+if [ -x "$NVCC" ]; then
+  "$NVCC" -std=c++20 -O3 -w -gencode arch=compute_100a,code=sm_100a -I"$R" -I"$R/include" -I"$R/Common" -I"$R/RayTracing" \
+      -DGLM_ENABLE_EXPERIMENTAL -Xcompiler -fPIC -shared -cudart static \
+      "$R/RayTracing/main_raytracing.cu" "$R/RayTracing/Random.cu" -o "$OUT/libref_gpu.so"
+  echo "built $OUT/libref_gpu.so"
+fi

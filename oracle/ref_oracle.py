@@ -139,3 +139,25 @@ def bench_render(scene, nodes, face_indices, cam60, cubemap, rng_states, surface
                            width, height, width * 16, frame_index, row_begin, row_stride, spp, bounces,
                            C.addressof(rays), C.addressof(threads))
     return s, rays.value, threads.value
+
+
+GPU_LIB_PATH = os.path.join(HERE, "_ref", "libref_gpu.so")
+_gpu_lib = None
+
+
+def gpu_available():
+    return os.path.exists(GPU_LIB_PATH)
+
+
+def gpu_lib():
+    """The reference's UNMODIFIED main_raytracing.cu + Random.cu built for sm_100a (oracle/build_ref.sh): its own
+    extern "C" raytracing_process / init_rng. Comparator only (tests, bench 'reference_cuda_kernel' note)."""
+    global _gpu_lib
+    if _gpu_lib is None:
+        h = C.CDLL(GPU_LIB_PATH, mode=os.RTLD_LOCAL | os.RTLD_NOW)
+        h.raytracing_process.restype = None
+        h.raytracing_process.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_void_p]
+        h.init_rng.restype = None
+        h.init_rng.argtypes = [C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint]
+        _gpu_lib = h
+    return _gpu_lib

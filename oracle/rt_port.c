@@ -140,11 +140,14 @@ static int port_bvh_hit(const PScene* s, v3 o, v3 d, PHit* result, int tie_mode,
     stack[sp++] = 0;
     const v3 nd = normalize(d);
     const float original = result->distance;
+    /* |d| < 1: the reference's cull is not conservative (Appendix A.4) and its result depends on its own visiting order;
+     * the lowest-id rule then only re-resolves exact ties among the candidates the reference order visits. */
+    const int order_independent = tie_mode && dot(d, d) >= 0.99999f;
     while (sp)
     {
         const PNode* node = &s->nodes[stack[--sp]];
         if (work) work[0]++;
-        if (!port_intersect_aabb(o, d, node->bmin, node->bmax, tie_mode ? original : result->distance)) continue;
+        if (!port_intersect_aabb(o, d, node->bmin, node->bmax, order_independent ? original : result->distance)) continue;
         if (node->prim_count > 0)
         {
             if (work) work[1] += node->prim_count;

@@ -81,6 +81,11 @@ def test_port_incoherent_rays_equal_reference_golden(pscene):
     g = golden("rays_kat.npz")
     ids, ts = pscene.trace_rays(g["rays"], True, 0)
     assert np.array_equal(ids, g["ids"]) and np.array_equal(ts.view(np.uint32), g["t"].view(np.uint32))
+    # lowest-id rule on arbitrary rays (incl. |d| < 1, where the reference's own visiting order decides what is found):
+    # same t bit for bit, ids only move down
+    ids1, ts1 = pscene.trace_rays(g["rays"], True, 1)
+    assert np.array_equal(ts1.view(np.uint32), ts.view(np.uint32)) and (ids1 <= ids).all()
+    assert np.array_equal(ids1, golden("primary_320x240_lowest_id.npz")["rays_id"])
 
 
 def test_port_fresh_rays_vs_live_reference(bunny, pscene, ref):

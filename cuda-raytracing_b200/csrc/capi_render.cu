@@ -60,6 +60,27 @@ namespace
         return RT_OK;
     }
 
+    // Work counters of the persistent kernels: a ring of device words per device, one slot per launch (launches in flight on
+    // different streams never share a slot unless more than kCounterSlots are outstanding).
+    constexpr int kCounterSlots = 256;
+    std::map<int, unsigned int*> g_counters;
+    unsigned g_counter_next = 0;
+    int NextCounter(unsigned int** out)
+    {
+        int dev = 0;
+        RT_CUDA(cudaGetDevice(&dev));
+        std::lock_guard<std::mutex> lock(g_mutex);
+        auto it = g_counters.find(dev);
+        if (it == g_counters.end())
+        {
+            unsigned int* d = nullptr;
+            RT_CUDA(cudaMalloc(&d, kCounterSlots * sizeof(unsigned int)));
+            it = g_counters.emplace(dev, d).first;
+        }
+        *out = it->second + (g_counter_next++ % kCounterSlots);
+        return RT_OK;
+    }
+
     const RtAccel* LookupAccel(const RtGPUScene* scene)
     {
         std::lock_guard<std::mutex> lock(g_mutex);
@@ -153,7 +174,14 @@ int rt_process_ex(const RtProcessParams* p)
     if (p->samples_per_launch <= 0 || p->max_bounces <= 0) return Fail(RT_E_INVALID, "rt_process_ex: spp and bounces must be positive");
     if (p->pitch < (uint64_t)p->width * 16) return Fail(RT_E_INVALID, "rt_process_ex: pitch smaller than a row");
     if (!p->scene->rng_state) return Fail(RT_E_INVALID, "rt_process_ex: scene has no rng_state");
-    if (p->variant != 0 && p->variant != 2) return Fail(RT_E_INVALID, "rt_process_ex: unknown variant");
+    if (p->variant < 0 || p->variant > 2) return Fail(RT_E_INVALID, "rt_process_ex: unknown variant");
+    if (p->variant == 1)
+    {
+        unsigned int* counter = nullptr;
+        if (int r = NextCounter(&counter)) return r;
+        RT_CUDA(LaunchPathTraceRegroup(p->accel->view, MakeSceneView(p->scene), *p, counter, (cudaStream_t)p->stream));
+        return RT_OK;
+    }
     RT_CUDA(LaunchPathTrace(p->accel->view, MakeSceneView(p->scene), *p, (cudaStream_t)p->stream));
     return RT_OK;
 }

@@ -32,6 +32,9 @@ cudaError_t LaunchCountWork(const AccelView& accel, const SceneView& scene, int 
                             uint32_t* d_counts, cudaStream_t stream);
 
 cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, const RtProcessParams& p, cudaStream_t stream);
+// variant 1: regrouping persistent kernel (pathtrace_regroup.cu); d_pixel_counter = one device uint owned by the caller for this launch
+cudaError_t LaunchPathTraceRegroup(const AccelView& accel, const SceneView& scene, const RtProcessParams& p, unsigned int* d_pixel_counter,
+                                   cudaStream_t stream);
 cudaError_t LaunchAmbientOcclusion(const AccelView& accel, const SceneView& scene, int width, int height, int ao_rays,
                                    float* d_ao, unsigned long long* d_ray_counter, cudaStream_t stream);
 cudaError_t LaunchTonemap(const void* surface, int width, int height, uint64_t pitch, float divide_by, uint8_t* d_rgba8,

@@ -108,7 +108,8 @@ typedef struct RtProcessParams
     int32_t max_bounces;        /* reference: 6  (main_raytracing.cu:115) */
     int32_t blend_mode;         /* 0 = reference running mean (lerp last->surface, weight 1/(frame+1));
                                    1 = surface += sum of this launch's samples (multi-GPU sum buffers) */
-    int32_t variant;            /* 0 = megakernel (regenerating), 1 = wavefront (per-bounce compaction),
+    int32_t variant;            /* 0 = megakernel (regenerating), 1 = regrouping persistent kernel (in-register wavefront:
+                                   finished rays are parked, shaded and refilled together by warp ballot; bit-identical image),
                                    2 = measurement: reference traversal order + d_work_counters (nodes popped, triangle tests) */
     int32_t write_last_frame;   /* 1 = also store the result into surface_last_frame (folds the reference's D2D copy) */
     const RtGPUScene* scene;    /* HOST struct, device pointers inside; rng_state must hold width*height states */

@@ -320,3 +320,24 @@ def test_against_reference_cuda_kernel_on_device(rt, torch_cuda, ref):
     assert close > 0.6, close
     assert block_rmse < 0.2, block_rmse
     assert abs(mean_ratio - 1) < 0.03, mean_ratio
+
+
+@pytest.mark.parametrize("size", [(64, 48), (37, 23), (200, 120)])
+def test_regroup_variant_bit_identical_to_megakernel(rt, torch_cuda, size):
+    """variant 1 (persistent, parked lanes shaded/refilled together by warp ballot, pixels pulled from a global counter) runs the
+    same per-pixel sequence of draws and fp32 operations as variant 0: surfaces, RNG states and ray counts are identical."""
+    t = torch_cuda
+    W, H = size
+    a = gpu_util.DeviceScene(rt, t, W, H, "poseB", seed=21, env=True)
+    b = gpu_util.DeviceScene(rt, t, W, H, "poseB", seed=21, env=True)
+    for f in range(2):
+        a.process(f, spp=7, bounces=4, variant=0, write_last=1)
+        b.process(f, spp=7, bounces=4, variant=1, write_last=1)
+    t.cuda.synchronize()
+    assert t.equal(a.surface, b.surface) and t.equal(a.last, b.last)
+    assert t.equal(a.rng, b.rng)
+    assert a.rays() == b.rays()
+    sa = t.zeros_like(a.surface); sb = t.zeros_like(a.surface)
+    a.process(0, spp=3, bounces=6, blend_mode=1, variant=0, surface=sa)
+    b.process(0, spp=3, bounces=6, blend_mode=1, variant=1, surface=sb)
+    assert t.equal(sa, sb)

@@ -36,7 +36,7 @@ UNIT = "Mrays/s"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--width", type=int, default=1920)
@@ -208,8 +208,9 @@ def run_b200_arm(a):
 
     d = gpu_util.DeviceScene(rt, torch, W, H, a.pose, seed=a.seed, env=True, device=dev)
     n_states = gpu_util.rng_state_count(W, H)
+    from cuda_raytracing_b200 import multigpu
     if world > 1:  # rank r owns cuRAND subsequences [r*n, (r+1)*n): disjoint streams, rank 0 == the 1-GPU stream
-        d.reseed(a.seed, rank * n_states)
+        d.reseed(a.seed, multigpu.rank_first_subsequence(rank, n_states))
     stream = torch.cuda.current_stream().cuda_stream
     from cuda_raytracing_b200.api import process_ex
 
@@ -238,8 +239,7 @@ def run_b200_arm(a):
         if blend == 1:
             sum_buf.zero_()
         frame(blend, sum_buf)
-        if world > 1:
-            dist.reduce(sum_buf, dst=0, op=dist.ReduceOp.SUM)
+        multigpu.reduce_frame(sum_buf, dist if world > 1 else None)
 
     for _ in range(max(a.warmup, 0)):
         flush.fill_(1); step()
@@ -259,8 +259,7 @@ def run_b200_arm(a):
             sum_buf.zero_()
         frame(blend, sum_buf)
         ev[k][1].record()      # kernel-only span (roofline)
-        if world > 1:
-            dist.reduce(sum_buf, dst=0, op=dist.ReduceOp.SUM)
+        multigpu.reduce_frame(sum_buf, dist if world > 1 else None)
         ev[k][2].record()
     torch.cuda.synchronize()
     if world > 1:

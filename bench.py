@@ -67,6 +67,10 @@ class CpuReference:
         if not ro.available():
             raise RuntimeError("oracle/_ref/libref_oracle.so missing (built by __graft_entry__.build() where /root/reference exists)")
         self.ro, self.a = ro, a
+        try:  # all host cores this process may use (torchrun sets OMP_NUM_THREADS=1 for its ranks)
+            ro.lib().ref_set_num_threads(len(os.sched_getaffinity(0)))
+        except (AttributeError, OSError):
+            pass
         rt = load_package()
         scene, _ = util.bunny_scene(rt)  # host-side assembly only (no device call)
         arr = scene.arrays()

@@ -147,7 +147,14 @@ int rt_trace_rays(const RtAccel* accel, const RtGPUScene* scene, const float* d_
                   int with_spheres, int variant, uint32_t* d_id, float* d_t, unsigned long long* d_ray_counter, void* stream)
 {
     if (!accel || !scene || (ray_count && (!d_rays || !d_id || !d_t))) return Fail(RT_E_INVALID, "rt_trace_rays: bad argument");
-    if (variant < 0 || variant > 1) return Fail(RT_E_INVALID, "rt_trace_rays: unknown variant");
+    if (variant < 0 || variant > 2) return Fail(RT_E_INVALID, "rt_trace_rays: unknown variant");
+    if (variant == 2)
+    {
+        unsigned int* counter = nullptr;
+        if (int r = NextCounter(&counter)) return r;
+        RT_CUDA(LaunchExtendRays(accel->view, MakeSceneView(scene), d_rays, ray_count, with_spheres != 0, d_id, d_t, d_ray_counter, counter, (cudaStream_t)stream));
+        return RT_OK;
+    }
     RT_CUDA(LaunchTraceRays(accel->view, MakeSceneView(scene), d_rays, ray_count, with_spheres != 0, variant, d_id, d_t, d_ray_counter, (cudaStream_t)stream));
     return RT_OK;
 }

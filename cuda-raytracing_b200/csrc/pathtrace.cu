@@ -9,6 +9,7 @@
 //   draws and fp32 operations is the reference's, so the stream and the image are reproduced.
 //   The XORWOW state lives in registers for the launch (reference: 24-B global RMW per draw).
 #include <cmath>
+#include <cstdlib>
 #include "shade.cuh"
 
 __device__ __forceinline__ void camera_ray_pt(const RtCamera& cam, float u, float v, Vec3& o, Vec3& d)
@@ -55,8 +56,8 @@ __device__ __forceinline__ void write_pixel(const FrameParams& P, int x, int y, 
 
 // kMode 0: product traversal. kMode 2: reference-order traversal with work counters (measurement of the
 // algorithmic bytes per ray; same image up to exact-tie resolution).
-template <int kMode>
-__global__ void __launch_bounds__(256) pathtrace_megakernel(AccelView A, SceneView S, FrameParams P)
+template <int kMode, int kMinBlocks>
+__global__ void __launch_bounds__(256, kMinBlocks) pathtrace_megakernel(AccelView A, SceneView S, FrameParams P)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int x = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
@@ -125,8 +126,13 @@ cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, cons
         P.consts.qz = cx * cy * sz - sx * sy * cz;
     }
     const dim3 grid((p.width + 15) / 16, (p.height + 15) / 16), block(256);
-    if (p.variant == 2) pathtrace_megakernel<2><<<grid, block, 0, stream>>>(accel, scene, P);
-    else pathtrace_megakernel<0><<<grid, block, 0, stream>>>(accel, scene, P);
+    static int min_blocks = 0;
+    if (!min_blocks) { const char* v = getenv("B200RT_MINBLOCKS"); min_blocks = v ? atoi(v) : 3; }  // occupancy sweep hook (profiles/)
+    if (p.variant == 2) pathtrace_megakernel<2, 3><<<grid, block, 0, stream>>>(accel, scene, P);
+    else if (min_blocks == 4) pathtrace_megakernel<0, 4><<<grid, block, 0, stream>>>(accel, scene, P);
+    else if (min_blocks == 5) pathtrace_megakernel<0, 5><<<grid, block, 0, stream>>>(accel, scene, P);
+    else if (min_blocks == 2) pathtrace_megakernel<0, 2><<<grid, block, 0, stream>>>(accel, scene, P);
+    else pathtrace_megakernel<0, 3><<<grid, block, 0, stream>>>(accel, scene, P);
     return cudaGetLastError();
 }
 

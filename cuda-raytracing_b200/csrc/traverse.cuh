@@ -103,7 +103,7 @@ __device__ __forceinline__ bool accept(float t, uint32_t key, const HitRecord& h
 
 template <bool kLazyExactBox, bool kTieById>
 __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, uint32_t count, Vec3 o, Vec3 d, Vec3 nd,
-                                           float start_length, HitRecord& h)
+                                           float start_length, HitRecord& h, uint32_t* verified_leaf = nullptr)
 {
     const TriRecord* tr = A.tris + first;
     for (uint32_t i = 0; i < count; i++)
@@ -115,8 +115,14 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
         const uint32_t key = kTieById ? id : __float_as_uint(r2.w);
         if (!accept(t, key, h)) continue;
         if (kLazyExactBox)
-        {   // the reference only tests this triangle if its leaf's box passes (main_raytracing.cu:46)
-            if (!exact_box(o, d, A.ref_nodes + __float_as_uint(r1.w), start_length)) continue;
+        {   // the reference only tests this triangle if its leaf's box passes (main_raytracing.cu:46); one-entry cache of the
+            // last leaf that passed (the smooth/flat duplicates of a face share a leaf and are accepted back to back)
+            const uint32_t leaf = __float_as_uint(r1.w);
+            if (!verified_leaf || *verified_leaf != leaf)
+            {
+                if (!exact_box(o, d, A.ref_nodes + leaf, start_length)) continue;
+                if (verified_leaf) *verified_leaf = leaf;
+            }
         }
         h.t = t; h.id = id; h.slot = first + i; h.key = key; h.bu = bu; h.bv = bv;
     }
@@ -129,15 +135,21 @@ template <bool kTieById>
 __device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, Vec3 nd, HitRecord& h)
 {
     const float start_length = h.t;
-    // reciprocal of the normalised direction; zero components -> huge finite (conservative)
+    // Conservative slab test in FMA form: t = fma(plane, inv, c) with inv = 1/nd (zero components -> huge finite) and
+    // c = -(o * inv). Its absolute error is bounded by ~3 ulp of |o * inv|; `slack` covers it and kWiden covers the relative
+    // part, so the cull accepts a superset of what the reference's division-based test accepts (DESIGN.md "box culls").
     const float big = 1e30f;
     const float ix = nd.x != 0.0f ? 1.0f / nd.x : big, iy = nd.y != 0.0f ? 1.0f / nd.y : big, iz = nd.z != 0.0f ? 1.0f / nd.z : big;
+    const float ax = o.x * ix, ay = o.y * iy, az = o.z * iz;
+    const float cx = -ax, cy = -ay, cz = -az;
+    const float slack = 4.0e-7f * fmaxf(fabsf(ax), fmaxf(fabsf(ay), fabsf(az))) + 1e-30f;
     const float kWiden = 1.0e-6f;
 
     uint32_t stack[RT_STACK_SIZE];
     int sp = 0;
     stack[sp++] = RT_SENTINEL;
     uint32_t node = A.root_ref;
+    uint32_t verified_leaf = RT_SENTINEL;
 
     while (node != RT_SENTINEL)
     {
@@ -147,22 +159,22 @@ __device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, V
             const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32);
             const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
             // child 0
-            float t1 = (a.x - o.x) * ix, t2 = (a.w - o.x) * ix;
+            float t1 = fmaf(a.x, ix, cx), t2 = fmaf(a.w, ix, cx);
             float mn0 = fminf(t1, t2), mx0 = fmaxf(t1, t2);
-            t1 = (a.y - o.y) * iy; t2 = (b.x - o.y) * iy;
-            mn0 = fmaxf(mn0, fminf(t1, t2)); mx0 = fminf(mx0, fmaxf(t1, t2));
-            t1 = (a.z - o.z) * iz; t2 = (b.y - o.z) * iz;
-            mn0 = fmaxf(mn0, fminf(t1, t2)); mx0 = fminf(mx0, fmaxf(t1, t2));
+            t1 = fmaf(a.y, iy, cy); t2 = fmaf(b.x, iy, cy);
+            float mnb = fminf(t1, t2), mxb = fmaxf(t1, t2);
+            t1 = fmaf(a.z, iz, cz); t2 = fmaf(b.y, iz, cz);
+            mn0 = fmaxf(fmaxf(mn0, mnb), fminf(t1, t2)); mx0 = fminf(fminf(mx0, mxb), fmaxf(t1, t2));
             // child 1
-            t1 = (b.z - o.x) * ix; t2 = (c.y - o.x) * ix;
+            t1 = fmaf(b.z, ix, cx); t2 = fmaf(c.y, ix, cx);
             float mn1 = fminf(t1, t2), mx1 = fmaxf(t1, t2);
-            t1 = (b.w - o.y) * iy; t2 = (c.z - o.y) * iy;
-            mn1 = fmaxf(mn1, fminf(t1, t2)); mx1 = fminf(mx1, fmaxf(t1, t2));
-            t1 = (c.x - o.z) * iz; t2 = (c.w - o.z) * iz;
-            mn1 = fmaxf(mn1, fminf(t1, t2)); mx1 = fminf(mx1, fmaxf(t1, t2));
-            // widen (superset of the reference's divisions), cull against the current best
-            const float lo0 = fmaf(-kWiden, fabsf(mn0), mn0), hi0 = fmaf(kWiden, fabsf(mx0), mx0);
-            const float lo1 = fmaf(-kWiden, fabsf(mn1), mn1), hi1 = fmaf(kWiden, fabsf(mx1), mx1);
+            t1 = fmaf(b.w, iy, cy); t2 = fmaf(c.z, iy, cy);
+            mnb = fminf(t1, t2); mxb = fmaxf(t1, t2);
+            t1 = fmaf(c.x, iz, cz); t2 = fmaf(c.w, iz, cz);
+            mn1 = fmaxf(fmaxf(mn1, mnb), fminf(t1, t2)); mx1 = fminf(fminf(mx1, mxb), fmaxf(t1, t2));
+            // widen, cull against the current best
+            const float lo0 = fmaf(-kWiden, fabsf(mn0), mn0) - slack, hi0 = fmaf(kWiden, fabsf(mx0), mx0) + slack;
+            const float lo1 = fmaf(-kWiden, fabsf(mn1), mn1) - slack, hi1 = fmaf(kWiden, fabsf(mx1), mx1) + slack;
             const bool hit0 = hi0 >= lo0 && lo0 <= h.t && hi0 > 0.0f;
             const bool hit1 = hi1 >= lo1 && lo1 <= h.t && hi1 > 0.0f;
             if (hit0 && hit1)
@@ -176,7 +188,7 @@ __device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, V
             else node = stack[--sp];
         }
         if (node == RT_SENTINEL) break;
-        leaf_tests<true, kTieById>(A, node & 0x07FFFFFFu, ((node >> 27) & 0xFu) + 1u, o, d, nd, start_length, h);
+        leaf_tests<true, kTieById>(A, node & 0x07FFFFFFu, ((node >> 27) & 0xFu) + 1u, o, d, nd, start_length, h, &verified_leaf);
         node = stack[--sp];
     }
 }

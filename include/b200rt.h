@@ -88,7 +88,8 @@ int rt_dds_read_level0(const char* dds_path, float* out_texels, size_t capacity_
 
 /* Pixel-centre primary rays of scene->camera (GPUCamera::GetRay, RayTracing/GPUScene.h:13).
  * d_id/d_t: width*height. with_spheres: also test scene->gpu_spheres first (GetRayHit semantics).
- * variant: 0 = product kernel, 1 = reference-order exact kernel (by-construction parity). */
+ * variant: 0 = product kernel, 1 = reference-order exact kernel (by-construction parity);
+ * rt_trace_rays also takes 2 = persistent extend kernel (dynamic ray fetch; same results as 0). */
 int rt_trace_primary(const RtAccel* accel, const RtGPUScene* scene, int width, int height, int with_spheres,
                      int variant, uint32_t* d_id, float* d_t, unsigned long long* d_ray_counter, void* stream);
 /* Arbitrary rays: 6 floats each (origin, direction as given; normalised inside like BVHRayHit does). */

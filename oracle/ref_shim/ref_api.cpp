@@ -56,6 +56,8 @@ REF_API uint32_t ref_sizeof(int which)
 }
 
 REF_API int ref_num_threads() { return omp_get_max_threads(); }
+// torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU-baseline legs ask for all host cores explicitly
+REF_API void ref_set_num_threads(int n) { if (n > 0) omp_set_num_threads(n); }
 
 // ---------------------------------------------------------------------------------------------
 // BVH: the reference builder, verbatim

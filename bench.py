@@ -127,7 +127,7 @@ def run_reference_arm(a):
             "dtype": "f32", "data": "synthetic", "config": {"workload": workload_name(a), "step": "bounded sample: " + cpu.sample_desc(stride, spp)},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "reference", "sample": cpu.sample_desc(stride, spp)},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    print_json(line)
     return 0
 
 
@@ -326,7 +326,7 @@ def run_b200_arm(a):
                                     "seconds": s}
         except Exception as e:  # the checker is optional on a box without the prebuilt oracle
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {e}"}
-    print(json.dumps(line), flush=True)
+    print_json(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -374,6 +374,16 @@ def run_e2e(a, rt, torch, dev, world, rank):
 
 def main():
     a = parse_args()
+    # The contract is ONE JSON line on stdout. Libraries (NCCL prints its version banner, torchrun its OMP notice) write to
+    # fd 1 too, so everything but the final line is routed to stderr: fd 1 is pointed at stderr for the run and the JSON line
+    # is written to the saved real stdout.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    global print_json
+    def print_json(line):
+        sys.stdout.flush()
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
     if a.impl == "reference":
         return run_reference_arm(a)
     return run_b200_arm(a)

@@ -13,7 +13,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libb200rt.so")
+LIB_PATH = os.environ.get("B200RT_LIB") or os.path.join(_HERE, "lib", "libb200rt.so")  # B200RT_LIB: A/B builds (build.py --out=)
 
 # numpy views of the reference-layout PODs (include/rt_types.h)
 VERTEX = np.dtype([("position", "<f4", 3), ("normal", "<f4", 3), ("uv", "<f4", 2)])

@@ -47,8 +47,12 @@ def needs_build():
     return not os.path.exists(LIB) or os.path.getmtime(LIB) < _newest_source_mtime()
 
 
-def build(force=False, verbose=False):
-    """Compile libb200rt.so for sm_100a. Returns the library path."""
+def build(force=False, verbose=False, defines=(), out=None):
+    """Compile libb200rt.so for sm_100a. Returns the library path. `defines`/`out`: A/B builds of tuning switches
+    (e.g. defines=["RT_TW_FMA=1"], out="libb200rt_fma.so"; select at run time with B200RT_LIB=<path>)."""
+    global LIB
+    if out:
+        force = True
     if not force and not needs_build():
         return LIB
     os.makedirs(LIB_DIR, exist_ok=True)
@@ -62,6 +66,11 @@ def build(force=False, verbose=False):
     ]
     if verbose:
         common += ["-Xptxas", "-v"]
+    common += ["-D" + d for d in defines]
+    target = os.path.join(LIB_DIR, out) if out else LIB
+    if out:
+        obj_dir = os.path.join(HERE, "build", out.replace(".so", ""))
+        os.makedirs(obj_dir, exist_ok=True)
     procs = []
     objects = []
     for src in SOURCES:
@@ -79,10 +88,12 @@ def build(force=False, verbose=False):
             sys.stderr.write(f"--- {src} ---\n{out}\n")
     if failed:
         raise RuntimeError("nvcc failed")
-    link = [_nvcc(), "-shared", "-o", LIB] + objects + ["-cudart", "static"]
+    link = [_nvcc(), "-shared", "-o", target] + objects + ["-cudart", "static"]
     subprocess.run(link, check=True)
-    return LIB
+    return target
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    defs = [a[2:] for a in sys.argv[1:] if a.startswith("-D")]
+    outs = [a[6:] for a in sys.argv[1:] if a.startswith("--out=")]
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, defines=defs, out=outs[0] if outs else None))

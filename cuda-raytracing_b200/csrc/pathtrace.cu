@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(256, kMinBlocks) pathtrace_megakernel(AccelVie
             const Vec3 nd = normalize3(ps.d);
             HitRecord h; h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
             sphere_tests(S.spheres, S.sphere_count, ps.o, nd, h);
-            if (kMode == 0) trace_wide<false>(A, ps.o, ps.d, nd, h);
+            if (kMode == 0) trace_wide<false, true>(A, ps.o, ps.d, nd, h);
             else trace_reference_order<false>(A, ps.o, ps.d, nd, h, &work_nodes, &work_tris);
             rays++;
             bool alive;
@@ -127,12 +127,12 @@ cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, cons
     }
     const dim3 grid((p.width + 15) / 16, (p.height + 15) / 16), block(256);
     static int min_blocks = 0;
-    if (!min_blocks) { const char* v = getenv("B200RT_MINBLOCKS"); min_blocks = v ? atoi(v) : 3; }  // occupancy sweep hook (profiles/)
+    if (!min_blocks) { const char* v = getenv("B200RT_MINBLOCKS"); min_blocks = v ? atoi(v) : 5; }  // occupancy sweep hook (profiles/)
     if (p.variant == 2) pathtrace_megakernel<2, 3><<<grid, block, 0, stream>>>(accel, scene, P);
     else if (min_blocks == 4) pathtrace_megakernel<0, 4><<<grid, block, 0, stream>>>(accel, scene, P);
-    else if (min_blocks == 5) pathtrace_megakernel<0, 5><<<grid, block, 0, stream>>>(accel, scene, P);
+    else if (min_blocks == 3) pathtrace_megakernel<0, 3><<<grid, block, 0, stream>>>(accel, scene, P);
     else if (min_blocks == 2) pathtrace_megakernel<0, 2><<<grid, block, 0, stream>>>(accel, scene, P);
-    else pathtrace_megakernel<0, 3><<<grid, block, 0, stream>>>(accel, scene, P);
+    else pathtrace_megakernel<0, 5><<<grid, block, 0, stream>>>(accel, scene, P);  // default: 5 resident CTAs/SM (48 regs, small spill) measured fastest
     return cudaGetLastError();
 }
 
@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(256) ambient_occlusion_kernel(AccelView A, Sce
             const Vec3 nd = normalize3(d);
             HitRecord h; h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
             sphere_tests(S.spheres, S.sphere_count, o, nd, h);
-            trace_wide<false>(A, o, d, nd, h);
+            trace_wide<false, true>(A, o, d, nd, h);
             rays++;
             if (k == 0)
             {

@@ -115,8 +115,8 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
         const uint32_t key = kTieById ? id : __float_as_uint(r2.w);
         if (!accept(t, key, h)) continue;
         if (kLazyExactBox)
-        {   // the reference only tests this triangle if its leaf's box passes (main_raytracing.cu:46); one-entry cache of the
-            // last leaf that passed (the smooth/flat duplicates of a face share a leaf and are accepted back to back)
+        {   // the reference only tests this triangle if its leaf's box passes (main_raytracing.cu:46); optional one-entry cache of
+            // the last leaf that passed (the smooth/flat duplicates of a face share a leaf and are accepted back to back)
             const uint32_t leaf = __float_as_uint(r1.w);
             if (!verified_leaf || *verified_leaf != leaf)
             {
@@ -131,25 +131,50 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
 // Product traversal: wide nodes, near-child-first, while-while, conservative box culls in
 // normalised units, exact leaf box re-check only on candidate hits.
 // `h` enters holding the sphere result (or a miss with t = 1e30).
-template <bool kTieById>
+// Tuning switches of trace_wide, A/B-measured on B200 (profiles/r01c_traversal_ab.txt); results are bit-identical either way.
+//   kFma (template): slab test as fma(plane, inv, -(o*inv)) + an absolute slack instead of (plane - o) * inv.
+//     Path-trace megakernel: 77.2 -> 74.9 ms/frame (72.3 with 5 resident CTAs/SM); bare trace_rays kernel: 5.13 -> 5.64 ms
+//     (the four extra live registers cost more than the 12 saved FADDs) => on for the path tracer, off for the query kernels.
+//   RT_TW_CACHE: one-entry cache of the last reference leaf whose exact box passed: slower (+2..3 %), off.
+//   RT_TW_TOS: top of the traversal stack in a register: neutral to slower, off.
+#ifndef RT_TW_CACHE
+#define RT_TW_CACHE 0
+#endif
+#ifndef RT_TW_TOS
+#define RT_TW_TOS 0
+#endif
+
+template <bool kTieById, bool kFma = false>
 __device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, Vec3 nd, HitRecord& h)
 {
     const float start_length = h.t;
-    // Conservative slab test in FMA form: t = fma(plane, inv, c) with inv = 1/nd (zero components -> huge finite) and
-    // c = -(o * inv). Its absolute error is bounded by ~3 ulp of |o * inv|; `slack` covers it and kWiden covers the relative
-    // part, so the cull accepts a superset of what the reference's division-based test accepts (DESIGN.md "box culls").
+    // reciprocal of the normalised direction; zero components -> huge finite (conservative)
     const float big = 1e30f;
     const float ix = nd.x != 0.0f ? 1.0f / nd.x : big, iy = nd.y != 0.0f ? 1.0f / nd.y : big, iz = nd.z != 0.0f ? 1.0f / nd.z : big;
+    const float kWiden = 1.0e-6f;
+    // kFma: abs error of fma(plane, inv, c) is bounded by ~3 ulp of |o * inv|: `slack` covers it, kWiden the relative part
     const float ax = o.x * ix, ay = o.y * iy, az = o.z * iz;
     const float cx = -ax, cy = -ay, cz = -az;
-    const float slack = 4.0e-7f * fmaxf(fabsf(ax), fmaxf(fabsf(ay), fabsf(az))) + 1e-30f;
-    const float kWiden = 1.0e-6f;
-
+    const float slack = kFma ? 4.0e-7f * fmaxf(fabsf(ax), fmaxf(fabsf(ay), fabsf(az))) + 1e-30f : 0.0f;
+#define RT_SLAB(p, inv, c, oc) (kFma ? fmaf(p, inv, c) : (((p) - (oc)) * (inv)))
     uint32_t stack[RT_STACK_SIZE];
     int sp = 0;
     stack[sp++] = RT_SENTINEL;
+#if RT_TW_TOS
+    uint32_t tos = RT_SENTINEL;
+#define RT_PUSH(x) do { stack[sp++] = tos; tos = (x); } while (0)
+#define RT_POP() (node = tos, tos = stack[--sp])
+#else
+#define RT_PUSH(x) do { stack[sp++] = (x); } while (0)
+#define RT_POP() (node = stack[--sp])
+#endif
     uint32_t node = A.root_ref;
-    uint32_t verified_leaf = RT_SENTINEL;
+#if RT_TW_CACHE
+    uint32_t verified = RT_SENTINEL;
+    uint32_t* const verified_ptr = &verified;
+#else
+    uint32_t* const verified_ptr = nullptr;
+#endif
 
     while (node != RT_SENTINEL)
     {
@@ -159,20 +184,20 @@ __device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, V
             const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32);
             const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
             // child 0
-            float t1 = fmaf(a.x, ix, cx), t2 = fmaf(a.w, ix, cx);
+            float t1 = RT_SLAB(a.x, ix, cx, o.x), t2 = RT_SLAB(a.w, ix, cx, o.x);
             float mn0 = fminf(t1, t2), mx0 = fmaxf(t1, t2);
-            t1 = fmaf(a.y, iy, cy); t2 = fmaf(b.x, iy, cy);
-            float mnb = fminf(t1, t2), mxb = fmaxf(t1, t2);
-            t1 = fmaf(a.z, iz, cz); t2 = fmaf(b.y, iz, cz);
-            mn0 = fmaxf(fmaxf(mn0, mnb), fminf(t1, t2)); mx0 = fminf(fminf(mx0, mxb), fmaxf(t1, t2));
+            t1 = RT_SLAB(a.y, iy, cy, o.y); t2 = RT_SLAB(b.x, iy, cy, o.y);
+            mn0 = fmaxf(mn0, fminf(t1, t2)); mx0 = fminf(mx0, fmaxf(t1, t2));
+            t1 = RT_SLAB(a.z, iz, cz, o.z); t2 = RT_SLAB(b.y, iz, cz, o.z);
+            mn0 = fmaxf(mn0, fminf(t1, t2)); mx0 = fminf(mx0, fmaxf(t1, t2));
             // child 1
-            t1 = fmaf(b.z, ix, cx); t2 = fmaf(c.y, ix, cx);
+            t1 = RT_SLAB(b.z, ix, cx, o.x); t2 = RT_SLAB(c.y, ix, cx, o.x);
             float mn1 = fminf(t1, t2), mx1 = fmaxf(t1, t2);
-            t1 = fmaf(b.w, iy, cy); t2 = fmaf(c.z, iy, cy);
-            mnb = fminf(t1, t2); mxb = fmaxf(t1, t2);
-            t1 = fmaf(c.x, iz, cz); t2 = fmaf(c.w, iz, cz);
-            mn1 = fmaxf(fmaxf(mn1, mnb), fminf(t1, t2)); mx1 = fminf(fminf(mx1, mxb), fmaxf(t1, t2));
-            // widen, cull against the current best
+            t1 = RT_SLAB(b.w, iy, cy, o.y); t2 = RT_SLAB(c.z, iy, cy, o.y);
+            mn1 = fmaxf(mn1, fminf(t1, t2)); mx1 = fminf(mx1, fmaxf(t1, t2));
+            t1 = RT_SLAB(c.x, iz, cz, o.z); t2 = RT_SLAB(c.w, iz, cz, o.z);
+            mn1 = fmaxf(mn1, fminf(t1, t2)); mx1 = fminf(mx1, fmaxf(t1, t2));
+            // widen (superset of the reference's divisions), cull against the current best
             const float lo0 = fmaf(-kWiden, fabsf(mn0), mn0) - slack, hi0 = fmaf(kWiden, fabsf(mx0), mx0) + slack;
             const float lo1 = fmaf(-kWiden, fabsf(mn1), mn1) - slack, hi1 = fmaf(kWiden, fabsf(mx1), mx1) + slack;
             const bool hit0 = hi0 >= lo0 && lo0 <= h.t && hi0 > 0.0f;
@@ -180,17 +205,20 @@ __device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, V
             if (hit0 && hit1)
             {
                 const bool swap = mn1 < mn0;
-                stack[sp++] = swap ? ch.x : ch.y;
+                RT_PUSH(swap ? ch.x : ch.y);
                 node = swap ? ch.y : ch.x;
             }
             else if (hit0) node = ch.x;
             else if (hit1) node = ch.y;
-            else node = stack[--sp];
+            else RT_POP();
         }
         if (node == RT_SENTINEL) break;
-        leaf_tests<true, kTieById>(A, node & 0x07FFFFFFu, ((node >> 27) & 0xFu) + 1u, o, d, nd, start_length, h, &verified_leaf);
-        node = stack[--sp];
+        leaf_tests<true, kTieById>(A, node & 0x07FFFFFFu, ((node >> 27) & 0xFu) + 1u, o, d, nd, start_length, h, verified_ptr);
+        RT_POP();
     }
+#undef RT_SLAB
+#undef RT_PUSH
+#undef RT_POP
 }
 
 // Reference-order traversal over the reference-layout nodes: right child first, exact box test at

@@ -341,3 +341,30 @@ def test_regroup_variant_bit_identical_to_megakernel(rt, torch_cuda, size):
     a.process(0, spp=3, bounces=6, blend_mode=1, variant=0, surface=sa)
     b.process(0, spp=3, bounces=6, blend_mode=1, variant=1, surface=sb)
     assert t.equal(sa, sb)
+
+
+def test_converged_image_rmse_vs_reference_at_1024spp(rt, torch_cuda):
+    """BASELINE.json's image bar: the path-traced image at ~1024 spp has RMSE <= 1 % of the reference's converged image.
+    Reference = the pinned plain-C port of raytracing_kernel_main (bit-identical to oracle/_ref) run live on the box's host cores:
+    205 progressive frames of 5 spp x 6 bounces (the reference's own frame protocol, RayTracing.cpp:205-235), same seed."""
+    import port_oracle as po
+    t = torch_cuda
+    W, H, FRAMES = 128, 96, 205
+    d = gpu_util.DeviceScene(rt, t, W, H, "poseB", seed=2024, env=True)
+    for f in range(FRAMES):
+        d.process(f, spp=5, bounces=6, write_last=1)
+    got = d.surface.cpu().numpy()
+    a = d.scene.arrays()
+    cam, _ = d.scene.camera()
+    ps = po.PortScene({k: util.raw(a[k]) for k in ("vertices", "faces", "spheres", "materials")}, util.raw(a["nodes"]), a["face_indices"],
+                      cam.view(np.uint8).ravel().copy(), util.cubemap_texels())
+    st = po.rng_init(gpu_util.rng_state_count(W, H), 2024)
+    surf = np.zeros((H, W, 4), np.float32); last = np.zeros((H, W, 4), np.float32)
+    for f in range(FRAMES):
+        ps.render(st, surf, last, W, H, f)
+        last[:] = surf
+    rmse = rel_rmse(got, surf)
+    with open(os.path.join(util.ROOT, "gpurun_out", "rmse_1024spp.txt"), "w") as fh:
+        fh.write(f"{W}x{H}, {FRAMES * 5} spp, 6 bounces, pose B: relative RMSE vs reference = {rmse:.5f}\n")
+    assert rmse <= 0.01, rmse
+    assert (got[..., 3] == 1).all()

@@ -1,3 +1,4 @@
+#include <algorithm>
 #include "Scene.h"
 #include "BVH.h"
 
@@ -53,8 +54,10 @@ namespace RayTracing
         const uint32_t index_offset = (uint32_t)vertices.size();
         const mat4 mesh_transform = transform * mesh.transform;
         const uint32_t nv = mesh.VertexCount(), nf = mesh.FaceCount();
-        vertices.reserve(vertices.size() + nv + size_t(nf) * 3);
-        faces.reserve(faces.size() + size_t(nf) * 2);
+        // geometric growth: an exact reserve per call would re-copy the whole scene for every instance of a mesh grid
+        const size_t need_v = vertices.size() + nv + size_t(nf) * 3, need_f = faces.size() + size_t(nf) * 2;
+        if (vertices.capacity() < need_v) vertices.reserve(std::max(need_v, vertices.capacity() * 2));
+        if (faces.capacity() < need_f) faces.reserve(std::max(need_f, faces.capacity() * 2));
         auto P = [&](uint32_t i) { return vec4(mesh.positions[3 * i], mesh.positions[3 * i + 1], mesh.positions[3 * i + 2], 1.0f); };
         for (uint32_t v = 0; v < nv; v++)
         {

@@ -296,6 +296,12 @@ def run_b200_arm(a):
         return 0
 
     peak, peak_src = measured_peaks()
+    traffic = None  # dram bytes per launch from the committed ncu capture of this exact launch shape (never measured under bench)
+    try:
+        if a.variant == 0 and (a.width, a.height, a.spp_per_launch, a.bounces, a.pose) == (1920, 1080, 64, 4, "poseB"):
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["pathtrace_megakernel"]["dram_bytes_per_launch"]
+    except Exception:
+        traffic = None
     launches = a.steps * launches_per_step
     px = W * H
     alg_bytes_per_launch = (rays / launches) * bytes_per_ray + px * 80.0
@@ -309,7 +315,7 @@ def run_b200_arm(a):
                    "parallelism": "1 GPU" if world == 1 else f"spp split: {world} ranks x {a.spp} spp, disjoint XORWOW subsequences, 1 NCCL reduce(sum fp32) of the frame per step",
                    "rays_per_step": rays_all / a.steps, "ms_per_frame_64spp": step_ms / a.steps, "wall_s": wall},
         "clocks": clocks, "gpu_launches": launches,
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "kernel": "pathtrace_megakernel", "peak_source": peak_src,
                      "bytes_per_ray": bytes_per_ray, "nodes_per_ray_reference_order": nodes_per_ray, "tris_per_ray_reference_order": tris_per_ray,
                      "note": "algorithmic bytes = rays x (32 B x nodes + 48 B x tris under the REFERENCE traversal order + 64) + pixels x 80; "

@@ -12,6 +12,14 @@ def _b(s):
     return None if s is None else str(s).encode()
 
 
+def _safe_destroy(name, handle):
+    """Destructors may run during interpreter shutdown, when module globals are already gone."""
+    try:
+        getattr(lib(), name)(handle)
+    except Exception:
+        pass
+
+
 class Mesh:
     """Loader::LoadedMesh (OBJ + smooth normals) - the stand-in for Loader::ImportScene (utils/AssimpLoader.cpp:29)."""
 
@@ -22,7 +30,7 @@ class Mesh:
 
     def __del__(self):
         if getattr(self, "handle", None):
-            lib().rt_host_mesh_destroy(self.handle)
+            _safe_destroy("rt_host_mesh_destroy", self.handle)
             self.handle = None
 
     def counts(self):
@@ -49,7 +57,7 @@ class Scene:
 
     def __del__(self):
         if getattr(self, "_owned", False) and getattr(self, "handle", None):
-            lib().rt_host_scene_destroy(self.handle)
+            _safe_destroy("rt_host_scene_destroy", self.handle)
             self.handle = None
 
     def setup_cornell_box(self):
@@ -133,7 +141,7 @@ class Accel:
 
     def __del__(self):
         if getattr(self, "handle", None):
-            lib().rt_accel_destroy(self.handle)
+            _safe_destroy("rt_accel_destroy", self.handle)
             self.handle = None
 
 
@@ -149,7 +157,7 @@ class EnvMap:
 
     def __del__(self):
         if getattr(self, "handle", None):
-            lib().rt_envmap_destroy(self.handle)
+            _safe_destroy("rt_envmap_destroy", self.handle)
             self.handle = None
 
 
@@ -191,7 +199,7 @@ class Tracer:
 
     def __del__(self):
         if getattr(self, "handle", None):
-            lib().rt_host_tracer_destroy(self.handle)
+            _safe_destroy("rt_host_tracer_destroy", self.handle)
             self.handle = None
 
 

@@ -61,7 +61,7 @@ def build(force=False, verbose=False, defines=(), out=None):
     common = [
         _nvcc(), "-std=c++20", "-O3", "-lineinfo", "-fmad=false",
         "-gencode", "arch=compute_100a,code=sm_100a",
-        "-Xcompiler", "-fPIC,-ffp-contract=off,-fvisibility=default,-Wall,-Wno-unused-function",
+        "-Xcompiler", "-fPIC,-ffp-contract=off,-fvisibility=default,-Wall,-Wno-unused-function,-fopenmp",
         "-I", os.path.join(ROOT, "include"), "-I", os.path.join(HERE, "csrc"), "-I", os.path.join(HERE, "host"),
     ]
     if verbose:
@@ -88,7 +88,7 @@ def build(force=False, verbose=False, defines=(), out=None):
             sys.stderr.write(f"--- {src} ---\n{out}\n")
     if failed:
         raise RuntimeError("nvcc failed")
-    link = [_nvcc(), "-shared", "-o", target] + objects + ["-cudart", "static"]
+    link = [_nvcc(), "-shared", "-o", target] + objects + ["-cudart", "static", "-Xcompiler", "-fopenmp", "-lgomp"]
     subprocess.run(link, check=True)
     return target
 

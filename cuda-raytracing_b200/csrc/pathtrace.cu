@@ -56,7 +56,7 @@ __device__ __forceinline__ void write_pixel(const FrameParams& P, int x, int y, 
 
 // kMode 0: product traversal. kMode 2: reference-order traversal with work counters (measurement of the
 // algorithmic bytes per ray; same image up to exact-tie resolution).
-template <int kMode, int kMinBlocks>
+template <int kMode, int kMinBlocks, bool kLockstep = false>
 __global__ void __launch_bounds__(256, kMinBlocks) pathtrace_megakernel(AccelView A, SceneView S, FrameParams P)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -65,6 +65,7 @@ __global__ void __launch_bounds__(256, kMinBlocks) pathtrace_megakernel(AccelVie
     const bool active = x < P.width && y < P.height;
     unsigned rays = 0;
     uint32_t work_nodes = 0, work_tris = 0;
+    const unsigned lane_mask = __ballot_sync(0xffffffffu, active);
     if (active)
     {
         RtRngState* state = S.rng_state + (size_t)y * P.width + x;  // GPUScene::GetRNGForPixel, GPUScene.h:95
@@ -73,8 +74,14 @@ __global__ void __launch_bounds__(256, kMinBlocks) pathtrace_megakernel(AccelVie
         PathState ps;
         int sample = 0, bounce = 0;
         bool fresh = true;
-        while (sample < P.spp)
+        while (kLockstep ? __any_sync(lane_mask, sample < P.spp) : (sample < P.spp))
         {
+            if (kLockstep)
+            {   // experiment: no regeneration across samples - a lane that finished its sample waits until the whole warp has
+                // (camera rays of one sample are then traced together, coherently)
+                const bool all_fresh = __all_sync(lane_mask, fresh);
+                if (sample >= P.spp || (fresh && !all_fresh)) continue;
+            }
             if (fresh)
             {   // main_raytracing.cu:190-191; jitter draws x first, then y
                 const float jx = rng.uniform(), jy = rng.uniform();
@@ -132,6 +139,7 @@ cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, cons
     else if (min_blocks == 4) pathtrace_megakernel<0, 4><<<grid, block, 0, stream>>>(accel, scene, P);
     else if (min_blocks == 3) pathtrace_megakernel<0, 3><<<grid, block, 0, stream>>>(accel, scene, P);
     else if (min_blocks == 2) pathtrace_megakernel<0, 2><<<grid, block, 0, stream>>>(accel, scene, P);
+    else if (getenv("B200RT_LOCKSTEP")) pathtrace_megakernel<0, 5, true><<<grid, block, 0, stream>>>(accel, scene, P);
     else pathtrace_megakernel<0, 5><<<grid, block, 0, stream>>>(accel, scene, P);  // default: 5 resident CTAs/SM (48 regs, small spill) measured fastest
     return cudaGetLastError();
 }

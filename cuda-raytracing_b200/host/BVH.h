@@ -2,8 +2,8 @@
 // same face-index permutation as RayTracing/BVH.cpp:8-124 (spatial-midpoint split on the node
 // bounds, longest axis first with the two-axis fallback, Hoare-style partition whose permutation
 // survives a failed axis, children numbered consecutively, left subtree numbered before right,
-// no leaf-size bound). Written iteratively (explicit work stack, pre-order) instead of the
-// reference's recursion so 14 M-triangle meshes cannot overflow the call stack.
+// no leaf-size bound). Built in parallel (OpenMP): level-synchronous top tree, depth-first
+// subtrees one thread each, then the reference's node numbering from subtree sizes - see BVH.cpp.
 #pragma once
 #include <cstdint>
 #include <span>
@@ -21,7 +21,7 @@ namespace RayTracing
         std::span<const uint32_t> GetFaceIndices() const { return face_indices; }
 
     private:
-        struct Centroid { float c[3]; uint32_t index; };
+        struct Centroid { float c[3]; uint32_t index; float lo[3], hi[3]; };  // centroid, face id, the triangle's own box
         void UpdateBounds(uint32_t node_index);
 
         std::vector<RtBVHNode> nodes;

@@ -143,6 +143,12 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
 #ifndef RT_TW_TOS
 #define RT_TW_TOS 0
 #endif
+#ifndef RT_TW_FOLD
+#define RT_TW_FOLD 0
+#endif
+#ifndef RT_TW_MODE
+#define RT_TW_MODE 0
+#endif
 
 template <bool kTieById, bool kFma = false>
 __device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, Vec3 nd, HitRecord& h)
@@ -176,46 +182,89 @@ __device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, V
     uint32_t* const verified_ptr = nullptr;
 #endif
 
+    // RT_TW_FOLD: the three culls (exit >= entry, entry <= best, exit > 0) as ONE compare max(entry, 0) <= widen(min(exit, best)):
+    // k1 = (1 + kWiden) / (1 - kWiden) and k2 = 2 slack / (1 - kWiden), both rounded up, move the whole widening onto the exit side,
+    // so the entry side needs none (a superset of the two-sided form term by term; -6 instructions per wide node).
+    const float k1 = 1.0f + 2.5e-6f, k2 = 2.1f * slack;
+#define RT_NODE_STEP()                                                                                                     \
+    do {                                                                                                                    \
+        const WideNode* w = A.wide + node;                                                                                  \
+        const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32); \
+        const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));                      \
+        float t1 = RT_SLAB(a.x, ix, cx, o.x), t2 = RT_SLAB(a.w, ix, cx, o.x);                                               \
+        float mn0 = fminf(t1, t2), mx0 = fmaxf(t1, t2);                                                                     \
+        t1 = RT_SLAB(a.y, iy, cy, o.y); t2 = RT_SLAB(b.x, iy, cy, o.y);                                                     \
+        mn0 = fmaxf(mn0, fminf(t1, t2)); mx0 = fminf(mx0, fmaxf(t1, t2));                                                   \
+        t1 = RT_SLAB(a.z, iz, cz, o.z); t2 = RT_SLAB(b.y, iz, cz, o.z);                                                     \
+        mn0 = fmaxf(mn0, fminf(t1, t2)); mx0 = fminf(mx0, fmaxf(t1, t2));                                                   \
+        t1 = RT_SLAB(b.z, ix, cx, o.x); t2 = RT_SLAB(c.y, ix, cx, o.x);                                                     \
+        float mn1 = fminf(t1, t2), mx1 = fmaxf(t1, t2);                                                                     \
+        t1 = RT_SLAB(b.w, iy, cy, o.y); t2 = RT_SLAB(c.z, iy, cy, o.y);                                                     \
+        mn1 = fmaxf(mn1, fminf(t1, t2)); mx1 = fminf(mx1, fmaxf(t1, t2));                                                   \
+        t1 = RT_SLAB(c.x, iz, cz, o.z); t2 = RT_SLAB(c.w, iz, cz, o.z);                                                     \
+        mn1 = fmaxf(mn1, fminf(t1, t2)); mx1 = fminf(mx1, fmaxf(t1, t2));                                                   \
+        bool hit0, hit1;                                                                                                    \
+        if (RT_TW_FOLD)                                                                                                     \
+        {                                                                                                                   \
+            hit0 = fmaxf(mn0, 0.0f) <= fmaf(fminf(mx0, h.t), k1, k2);                                                       \
+            hit1 = fmaxf(mn1, 0.0f) <= fmaf(fminf(mx1, h.t), k1, k2);                                                       \
+        }                                                                                                                   \
+        else                                                                                                                \
+        {   /* widen (superset of the reference's divisions), cull against the current best */                             \
+            const float lo0 = fmaf(-kWiden, fabsf(mn0), mn0) - slack, hi0 = fmaf(kWiden, fabsf(mx0), mx0) + slack;          \
+            const float lo1 = fmaf(-kWiden, fabsf(mn1), mn1) - slack, hi1 = fmaf(kWiden, fabsf(mx1), mx1) + slack;          \
+            hit0 = hi0 >= lo0 && lo0 <= h.t && hi0 > 0.0f;                                                                  \
+            hit1 = hi1 >= lo1 && lo1 <= h.t && hi1 > 0.0f;                                                                  \
+        }                                                                                                                   \
+        if (hit0 && hit1)                                                                                                   \
+        {                                                                                                                   \
+            const bool swap = mn1 < mn0;                                                                                    \
+            RT_PUSH(swap ? ch.x : ch.y);                                                                                    \
+            node = swap ? ch.y : ch.x;                                                                                      \
+        }                                                                                                                   \
+        else if (hit0) node = ch.x;                                                                                         \
+        else if (hit1) node = ch.y;                                                                                         \
+        else RT_POP();                                                                                                      \
+    } while (0)
+#define RT_LEAF_STEP(ref) leaf_tests<true, kTieById>(A, (ref) & 0x07FFFFFFu, (((ref) >> 27) & 0xFu) + 1u, o, d, nd, start_length, h, verified_ptr)
+
+#if RT_TW_MODE == 1
+    // if-if: one node of either kind per iteration, no inner loop to wait in
     while (node != RT_SENTINEL)
     {
-        while (!(node & RT_LEAF_BIT))
+        if (!(node & RT_LEAF_BIT)) RT_NODE_STEP();
+        else { RT_LEAF_STEP(node); RT_POP(); }
+    }
+#elif RT_TW_MODE == 2
+    // while-while with one postponed leaf: a lane that reaches a leaf keeps descending until it holds two (or runs dry)
+    while (node != RT_SENTINEL)
+    {
+        uint32_t pending = RT_SENTINEL;
+        while (true)
         {
-            const WideNode* w = A.wide + node;
-            const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32);
-            const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
-            // child 0
-            float t1 = RT_SLAB(a.x, ix, cx, o.x), t2 = RT_SLAB(a.w, ix, cx, o.x);
-            float mn0 = fminf(t1, t2), mx0 = fmaxf(t1, t2);
-            t1 = RT_SLAB(a.y, iy, cy, o.y); t2 = RT_SLAB(b.x, iy, cy, o.y);
-            mn0 = fmaxf(mn0, fminf(t1, t2)); mx0 = fminf(mx0, fmaxf(t1, t2));
-            t1 = RT_SLAB(a.z, iz, cz, o.z); t2 = RT_SLAB(b.y, iz, cz, o.z);
-            mn0 = fmaxf(mn0, fminf(t1, t2)); mx0 = fminf(mx0, fmaxf(t1, t2));
-            // child 1
-            t1 = RT_SLAB(b.z, ix, cx, o.x); t2 = RT_SLAB(c.y, ix, cx, o.x);
-            float mn1 = fminf(t1, t2), mx1 = fmaxf(t1, t2);
-            t1 = RT_SLAB(b.w, iy, cy, o.y); t2 = RT_SLAB(c.z, iy, cy, o.y);
-            mn1 = fmaxf(mn1, fminf(t1, t2)); mx1 = fminf(mx1, fmaxf(t1, t2));
-            t1 = RT_SLAB(c.x, iz, cz, o.z); t2 = RT_SLAB(c.w, iz, cz, o.z);
-            mn1 = fmaxf(mn1, fminf(t1, t2)); mx1 = fminf(mx1, fmaxf(t1, t2));
-            // widen (superset of the reference's divisions), cull against the current best
-            const float lo0 = fmaf(-kWiden, fabsf(mn0), mn0) - slack, hi0 = fmaf(kWiden, fabsf(mx0), mx0) + slack;
-            const float lo1 = fmaf(-kWiden, fabsf(mn1), mn1) - slack, hi1 = fmaf(kWiden, fabsf(mx1), mx1) + slack;
-            const bool hit0 = hi0 >= lo0 && lo0 <= h.t && hi0 > 0.0f;
-            const bool hit1 = hi1 >= lo1 && lo1 <= h.t && hi1 > 0.0f;
-            if (hit0 && hit1)
+            if (node == RT_SENTINEL) break;
+            if (node & RT_LEAF_BIT)
             {
-                const bool swap = mn1 < mn0;
-                RT_PUSH(swap ? ch.x : ch.y);
-                node = swap ? ch.y : ch.x;
+                if (pending != RT_SENTINEL) break;
+                pending = node; RT_POP();
+                continue;
             }
-            else if (hit0) node = ch.x;
-            else if (hit1) node = ch.y;
-            else RT_POP();
+            RT_NODE_STEP();
         }
+        if (pending != RT_SENTINEL) RT_LEAF_STEP(pending);
+        if (node != RT_SENTINEL) { RT_LEAF_STEP(node); RT_POP(); }
+    }
+#else
+    while (node != RT_SENTINEL)
+    {
+        while (!(node & RT_LEAF_BIT)) RT_NODE_STEP();
         if (node == RT_SENTINEL) break;
-        leaf_tests<true, kTieById>(A, node & 0x07FFFFFFu, ((node >> 27) & 0xFu) + 1u, o, d, nd, start_length, h, verified_ptr);
+        RT_LEAF_STEP(node);
         RT_POP();
     }
+#endif
+#undef RT_NODE_STEP
+#undef RT_LEAF_STEP
 #undef RT_SLAB
 #undef RT_PUSH
 #undef RT_POP

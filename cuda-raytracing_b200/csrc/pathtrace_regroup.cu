@@ -7,7 +7,10 @@
 //   * every lane is a small state machine {NEED, TRAV, DONE}. A lane whose ray ended does NOT shade at once (that would
 //     run the ~400-instruction shade/regenerate code with one lane active); it parks in NEED. By warp ballot, the parked
 //     lanes are shaded + refilled together as soon as kRefill of them are waiting (or nobody is traversing any more);
-//   * traversal runs in while-while segments (inner chain -> one leaf) for all TRAV lanes between regroup points.
+//   * traversal is if-if: every TRAV lane does ONE step per loop iteration - a wide node, or one triangle of a leaf (the
+//     leaf reference is re-encoded with its remaining range) - so no lane waits in an inner loop and the regroup vote is
+//     taken after every step. (Round-1 first version: voted inner/leaf phases with postponed leaves - SIMT efficiency 13.8
+//     but +60 % thread-level work, slower than the megakernel)
 //
 // Per pixel, the order of RNG draws and fp32 operations is exactly the megakernel's (and so the reference's): the image is
 // bit-identical to variant 0 (tests/test_gpu_parity.py::test_regroup_variant_bit_identical_to_megakernel).
@@ -27,13 +30,12 @@ namespace
         int frame_index, spp, max_bounces, blend_mode, write_last;
         unsigned long long* ray_counter;
         unsigned int* pixel_counter;  // zeroed before the launch
-        int refill, leaf_batch;       // regroup thresholds (lanes)
+        int refill;                   // regroup threshold (lanes)
         PathConsts consts;
     };
 
     enum : int { ST_NEED = 0, ST_TRAV = 1, ST_DONE = 2 };
     constexpr int kRefill = 12;     // shade/refill as soon as this many lanes are parked
-    constexpr int kLeafBatch = 12;  // run the triangle tests as soon as this many lanes hold a postponed leaf
 
     __device__ __forceinline__ void camera_ray_rg(const RtCamera& cam, float u, float v, Vec3& o, Vec3& d)
     {
@@ -66,30 +68,8 @@ namespace
     }
 }
 
-// Lazily exact leaf test with a one-entry cache of the last reference leaf whose exact box passed for this ray
-// (the smooth/flat duplicates of a bunny face share a leaf: the second acceptance does not redo the 6 divisions).
-__device__ __forceinline__ void leaf_tests_cached(const AccelView& A, uint32_t first, uint32_t count, Vec3 o, Vec3 d, Vec3 nd,
-                                                  float start_length, HitRecord& h, uint32_t& verified_leaf)
-{
-    const TriRecord* tr = A.tris + first;
-    for (uint32_t i = 0; i < count; i++)
-    {
-        const float4 r0 = ldg4(&tr[i]), r1 = ldg4(reinterpret_cast<const char*>(&tr[i]) + 16), r2 = ldg4(reinterpret_cast<const char*>(&tr[i]) + 32);
-        float t, bu, bv;
-        if (!tri_test(o, nd, r0, r1, r2, t, bu, bv)) continue;
-        const uint32_t key = __float_as_uint(r2.w);  // original slot = the reference's visiting order inside a leaf
-        if (!accept(t, key, h)) continue;
-        const uint32_t leaf = __float_as_uint(r1.w);
-        if (leaf != verified_leaf)
-        {   // the reference only tests this triangle if its leaf's box passes (main_raytracing.cu:46)
-            if (!exact_box(o, d, A.ref_nodes + leaf, start_length)) continue;
-            verified_leaf = leaf;
-        }
-        h.t = t; h.id = __float_as_uint(r0.w); h.slot = first + i; h.key = key; h.bu = bu; h.bv = bv;
-    }
-}
-
-__global__ void __launch_bounds__(256, 3) pathtrace_regroup_kernel(AccelView A, SceneView S, RegroupParams P)
+template <int kMinBlocks>
+__global__ void __launch_bounds__(256, kMinBlocks) pathtrace_regroup_kernel(AccelView A, SceneView S, RegroupParams P)
 {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -105,14 +85,12 @@ __global__ void __launch_bounds__(256, 3) pathtrace_regroup_kernel(AccelView A, 
     HitRecord h; h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
     Vec3 nd = mk3(0, 0, 1);
     // conservative slab test in FMA form: t = fma(plane, inv, c), c = -(o * inv); abs error <= slack (see DESIGN.md "box culls")
-    float ix = 0, iy = 0, iz = 0, cx = 0, cy = 0, cz = 0, slack = 0, start_length = 1e30f;
-    uint32_t node = RT_SENTINEL;     // current INNER node (or sentinel); leaves never sit here or on the stack
-    uint32_t pend0 = 0, pend1 = 0, pend2 = 0; int npend = 0;  // postponed leaves (speculative traversal)
-    uint32_t verified_leaf = RT_SENTINEL;
+    float ix = 0, iy = 0, iz = 0, cx = 0, cy = 0, cz = 0, k2 = 0, start_length = 1e30f;
+    uint32_t node = RT_SENTINEL;     // current node reference (inner, leaf with its remaining range, or sentinel)
     int sp = 0;
     uint32_t stack[RT_STACK_SIZE];
     unsigned rays = 0;
-    const float kWiden = 1.0e-6f, big = 1e30f;
+    const float kFoldK1 = 1.0f + 2.5e-6f, big = 1e30f;
 
     for (;;)
     {
@@ -183,66 +161,55 @@ __global__ void __launch_bounds__(256, 3) pathtrace_regroup_kernel(AccelView A, 
                 ix = nd.x != 0.0f ? 1.0f / nd.x : big; iy = nd.y != 0.0f ? 1.0f / nd.y : big; iz = nd.z != 0.0f ? 1.0f / nd.z : big;
                 const float ax = ps.o.x * ix, ay = ps.o.y * iy, az = ps.o.z * iz;
                 cx = -ax; cy = -ay; cz = -az;
-                slack = 4.0e-7f * fmaxf(fabsf(ax), fmaxf(fabsf(ay), fabsf(az))) + 1e-30f;
-                sp = 0; stack[sp++] = RT_SENTINEL; npend = 0; verified_leaf = RT_SENTINEL;
+                k2 = 2.1f * (4.0e-7f * fmaxf(fabsf(ax), fmaxf(fabsf(ay), fabsf(az))) + 1e-30f);
+                sp = 0; stack[sp++] = RT_SENTINEL;
                 node = A.root_ref;
-                if (node & RT_LEAF_BIT) { pend0 = node; npend = 1; node = RT_SENTINEL; }  // degenerate one-leaf tree
                 state = ST_TRAV; rays++;
             }
         }
 
-        // ---------------- inner phase: one wide node for every lane that has one and room for two more leaves ----------------
-        const bool can_inner = state == ST_TRAV && node != RT_SENTINEL && npend <= 1;
-        if (can_inner)
+        // ---------------- traversal: ONE step per lane and iteration, if-if (a wide node, or one triangle of a leaf) ----------------
+        // No inner loop to wait in and nothing speculative: the per-ray work is the megakernel's, node for node.
+        if (state == ST_TRAV)
         {
-            const WideNode* w = A.wide + node;
-            const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32);
-            const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
-            float t1 = fmaf(a.x, ix, cx), t2 = fmaf(a.w, ix, cx);
-            float mn0 = fminf(t1, t2), mx0 = fmaxf(t1, t2);
-            t1 = fmaf(a.y, iy, cy); t2 = fmaf(b.x, iy, cy);
-            float mnb = fminf(t1, t2), mxb = fmaxf(t1, t2);
-            t1 = fmaf(a.z, iz, cz); t2 = fmaf(b.y, iz, cz);
-            mn0 = fmaxf(fmaxf(mn0, mnb), fminf(t1, t2)); mx0 = fminf(fminf(mx0, mxb), fmaxf(t1, t2));
-            t1 = fmaf(b.z, ix, cx); t2 = fmaf(c.y, ix, cx);
-            float mn1 = fminf(t1, t2), mx1 = fmaxf(t1, t2);
-            t1 = fmaf(b.w, iy, cy); t2 = fmaf(c.z, iy, cy);
-            mnb = fminf(t1, t2); mxb = fmaxf(t1, t2);
-            t1 = fmaf(c.x, iz, cz); t2 = fmaf(c.w, iz, cz);
-            mn1 = fmaxf(fmaxf(mn1, mnb), fminf(t1, t2)); mx1 = fminf(fminf(mx1, mxb), fmaxf(t1, t2));
-            const float lo0 = fmaf(-kWiden, fabsf(mn0), mn0) - slack, hi0 = fmaf(kWiden, fabsf(mx0), mx0) + slack;
-            const float lo1 = fmaf(-kWiden, fabsf(mn1), mn1) - slack, hi1 = fmaf(kWiden, fabsf(mx1), mx1) + slack;
-            const bool hit0 = hi0 >= lo0 && lo0 <= h.t && hi0 > 0.0f;
-            const bool hit1 = hi1 >= lo1 && lo1 <= h.t && hi1 > 0.0f;
-            // leaves are postponed, inner children are visited near-first
-            const bool leaf0 = hit0 && (ch.x & RT_LEAF_BIT), leaf1 = hit1 && (ch.y & RT_LEAF_BIT);
-            const bool in0 = hit0 && !(ch.x & RT_LEAF_BIT), in1 = hit1 && !(ch.y & RT_LEAF_BIT);
-            if (leaf0) { if (npend == 0) pend0 = ch.x; else pend1 = ch.x; npend++; }
-            if (leaf1) { if (npend == 0) pend0 = ch.y; else if (npend == 1) pend1 = ch.y; else pend2 = ch.y; npend++; }
-            if (in0 && in1)
+            if (!(node & RT_LEAF_BIT))
             {
-                const bool swap = mn1 < mn0;
-                stack[sp++] = swap ? ch.x : ch.y;
-                node = swap ? ch.y : ch.x;
+                const WideNode* w = A.wide + node;
+                const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32);
+                const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
+                float t1 = fmaf(a.x, ix, cx), t2 = fmaf(a.w, ix, cx);
+                float mn0 = fminf(t1, t2), mx0 = fmaxf(t1, t2);
+                t1 = fmaf(a.y, iy, cy); t2 = fmaf(b.x, iy, cy);
+                float mnb = fminf(t1, t2), mxb = fmaxf(t1, t2);
+                t1 = fmaf(a.z, iz, cz); t2 = fmaf(b.y, iz, cz);
+                mn0 = fmaxf(fmaxf(mn0, mnb), fminf(t1, t2)); mx0 = fminf(fminf(mx0, mxb), fmaxf(t1, t2));
+                t1 = fmaf(b.z, ix, cx); t2 = fmaf(c.y, ix, cx);
+                float mn1 = fminf(t1, t2), mx1 = fmaxf(t1, t2);
+                t1 = fmaf(b.w, iy, cy); t2 = fmaf(c.z, iy, cy);
+                mnb = fminf(t1, t2); mxb = fmaxf(t1, t2);
+                t1 = fmaf(c.x, iz, cz); t2 = fmaf(c.w, iz, cz);
+                mn1 = fmaxf(fmaxf(mn1, mnb), fminf(t1, t2)); mx1 = fminf(fminf(mx1, mxb), fmaxf(t1, t2));
+                // folded conservative cull (traverse.cuh, RT_TW_FOLD): max(entry, 0) <= widen(min(exit, best))
+                const bool hit0 = fmaxf(mn0, 0.0f) <= fmaf(fminf(mx0, h.t), kFoldK1, k2);
+                const bool hit1 = fmaxf(mn1, 0.0f) <= fmaf(fminf(mx1, h.t), kFoldK1, k2);
+                if (hit0 && hit1)
+                {
+                    const bool swap = mn1 < mn0;
+                    stack[sp++] = swap ? ch.x : ch.y;
+                    node = swap ? ch.y : ch.x;
+                }
+                else if (hit0) node = ch.x;
+                else if (hit1) node = ch.y;
+                else node = stack[--sp];
             }
-            else if (in0) node = ch.x;
-            else if (in1) node = ch.y;
-            else node = stack[--sp];
-        }
-
-        // ---------------- leaf phase: when enough lanes hold a postponed leaf, or nobody can descend any further ----------------
-        const unsigned m_pend = __ballot_sync(FULL, state == ST_TRAV && npend > 0);
-        const unsigned m_inner = __ballot_sync(FULL, state == ST_TRAV && node != RT_SENTINEL && npend <= 1);
-        if (m_pend && (__popc(m_pend) >= P.leaf_batch || m_inner == 0u))
-        {
-            if (state == ST_TRAV && npend > 0)
-            {
-                npend--;
-                const uint32_t leaf = npend == 0 ? pend0 : (npend == 1 ? pend1 : pend2);
-                leaf_tests_cached(A, leaf & 0x07FFFFFFu, ((leaf >> 27) & 0xFu) + 1u, ps.o, ps.d, nd, start_length, h, verified_leaf);
+            else
+            {   // one triangle; the leaf reference is re-encoded with the remaining range
+                leaf_tests<true, false>(A, node & 0x07FFFFFFu, 1u, ps.o, ps.d, nd, start_length, h);
+                if (node & 0x78000000u) node = node - (1u << 27) + 1u;
+                else node = stack[--sp];
             }
+            if (node == RT_SENTINEL) { state = ST_NEED; have_hit = true; }
         }
-        if (state == ST_TRAV && node == RT_SENTINEL && npend == 0) { state = ST_NEED; have_hit = true; }
     }
 
     if (P.ray_counter)
@@ -261,9 +228,8 @@ cudaError_t LaunchPathTraceRegroup(const AccelView& accel, const SceneView& scen
     P.width = p.width; P.height = p.height; P.pitch = p.pitch; P.frame_index = p.frame_index;
     P.spp = p.samples_per_launch; P.max_bounces = p.max_bounces; P.blend_mode = p.blend_mode; P.write_last = p.write_last_frame;
     P.ray_counter = p.d_ray_counter; P.pixel_counter = d_pixel_counter;
-    P.refill = kRefill; P.leaf_batch = kLeafBatch;
+    P.refill = kRefill;
     if (const char* v = getenv("B200RT_REFILL")) P.refill = atoi(v);        // tuning hooks (profiles/ sweeps)
-    if (const char* v = getenv("B200RT_LEAF_BATCH")) P.leaf_batch = atoi(v);
     {   // glm quat(vec3(0, PI, 0)), type_quat.inl:204-213, in host fp32 like the oracle
         const float PI = 3.1415926536f;
         const float cx = std::cos(0.0f * 0.5f), cy = std::cos(PI * 0.5f), cz = std::cos(0.0f * 0.5f);
@@ -275,13 +241,18 @@ cudaError_t LaunchPathTraceRegroup(const AccelView& accel, const SceneView& scen
     }
     cudaError_t e = cudaMemsetAsync(d_pixel_counter, 0, sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;
-    static int blocks_per_sm = 0, sm_count = 0;  // persistent grid: one resident wave
+    static int blocks_per_sm = 0, sm_count = 0, min_blocks = 0;  // persistent grid: one resident wave
     if (!blocks_per_sm)
     {
         int dev = 0;
         if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
         if ((e = cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
-        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, pathtrace_regroup_kernel, 256, 0)) != cudaSuccess) return e;
+        const char* v = getenv("B200RT_RG_MINBLOCKS");  // occupancy sweep hook (profiles/)
+        min_blocks = v ? atoi(v) : 3;
+        if (min_blocks == 4) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, pathtrace_regroup_kernel<4>, 256, 0);
+        else if (min_blocks == 5) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, pathtrace_regroup_kernel<5>, 256, 0);
+        else e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, pathtrace_regroup_kernel<3>, 256, 0);
+        if (e != cudaSuccess) return e;
         if (blocks_per_sm < 1) blocks_per_sm = 1;
     }
     const unsigned tiles = (unsigned)((p.width + 7) / 8) * (unsigned)((p.height + 3) / 4);
@@ -289,6 +260,8 @@ cudaError_t LaunchPathTraceRegroup(const AccelView& accel, const SceneView& scen
     const unsigned needed = (tiles + 7) / 8;  // 8 warps per block
     if (grid > needed) grid = needed;
     if (grid < 1) grid = 1;
-    pathtrace_regroup_kernel<<<grid, 256, 0, stream>>>(accel, scene, P);
+    if (min_blocks == 4) pathtrace_regroup_kernel<4><<<grid, 256, 0, stream>>>(accel, scene, P);
+    else if (min_blocks == 5) pathtrace_regroup_kernel<5><<<grid, 256, 0, stream>>>(accel, scene, P);
+    else pathtrace_regroup_kernel<3><<<grid, 256, 0, stream>>>(accel, scene, P);
     return cudaGetLastError();
 }

@@ -144,10 +144,10 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
 #define RT_TW_TOS 0
 #endif
 #ifndef RT_TW_FOLD
-#define RT_TW_FOLD 0
+#define RT_TW_FOLD 1
 #endif
 #ifndef RT_TW_MODE
-#define RT_TW_MODE 0
+#define RT_TW_MODE 3
 #endif
 
 template <bool kTieById, bool kFma = false>
@@ -233,6 +233,29 @@ __device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, V
     while (node != RT_SENTINEL)
     {
         if (!(node & RT_LEAF_BIT)) RT_NODE_STEP();
+        else { RT_LEAF_STEP(node); RT_POP(); }
+    }
+#elif RT_TW_MODE == 3
+    // if-if, one TRIANGLE per iteration: the leaf reference is re-encoded with the remaining range, no extra state
+    while (node != RT_SENTINEL)
+    {
+        if (!(node & RT_LEAF_BIT)) RT_NODE_STEP();
+        else
+        {
+            leaf_tests<true, kTieById>(A, node & 0x07FFFFFFu, 1u, o, d, nd, start_length, h, verified_ptr);
+            if (node & 0x78000000u) node = node - (1u << 27) + 1u;
+            else RT_POP();
+        }
+    }
+#elif RT_TW_MODE == 5
+    // if-if with up to two wide nodes per iteration (a 2-triangle leaf costs about two node steps)
+    while (node != RT_SENTINEL)
+    {
+        if (!(node & RT_LEAF_BIT))
+        {
+            RT_NODE_STEP();
+            if (node != RT_SENTINEL && !(node & RT_LEAF_BIT)) RT_NODE_STEP();
+        }
         else { RT_LEAF_STEP(node); RT_POP(); }
     }
 #elif RT_TW_MODE == 2

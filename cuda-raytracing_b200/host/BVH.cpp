@@ -1,5 +1,6 @@
 #include "BVH.h"
 #include <algorithm>
+#include <memory>
 #include <numeric>
 #include <chrono>
 #include <cstdio>
@@ -30,8 +31,6 @@ namespace RayTracing
         constexpr uint32_t kSubtree = 1u << 14;  // nodes at or below this size are finished depth-first by one thread
     }
 
-    void BVH::UpdateBounds(uint32_t) {}  // (kept for interface compatibility; bounds are computed by BoundsOf)
-
     void BVH::Calculate(std::span<const RtVertex> vertices_, std::span<const RtFace> faces_)
     {
         vertices = vertices_; faces = faces_;
@@ -53,13 +52,26 @@ namespace RayTracing
         struct Temp { float lo[3], hi[3]; uint32_t first, count, left; };  // left = temp id of the first child (right = left + 1), 0 = leaf
         std::vector<Temp> temp; temp.reserve(1024);
 
-        auto bounds_of = [&](uint32_t first, uint32_t count, float* lo, float* hi, bool parallel)
-        {   // RayTracing/BVH.cpp:45-57 (min/max over the node's vertices; exact in any grouping)
+        // RayTracing/BVH.cpp:45-57 (min/max over the node's vertices; exact in any grouping). The per-triangle box travels
+        // with the centroid: no vertex gathers here. Two forms: an OpenMP region costs about a microsecond even when it runs
+        // on one thread, and there are as many small nodes as triangles.
+        auto bounds_serial = [&](uint32_t first, uint32_t count, float* lo, float* hi)
+        {
             float l0 = 1e30f, l1 = 1e30f, l2 = 1e30f, h0 = -1e30f, h1 = -1e30f, h2 = -1e30f;
-#pragma omp parallel for schedule(static) reduction(min : l0, l1, l2) reduction(max : h0, h1, h2) if (parallel)
+            for (const Centroid* t = triangles.data() + first, *e = t + count; t != e; ++t)
+            {
+                l0 = std::min(l0, t->lo[0]); l1 = std::min(l1, t->lo[1]); l2 = std::min(l2, t->lo[2]);
+                h0 = std::max(h0, t->hi[0]); h1 = std::max(h1, t->hi[1]); h2 = std::max(h2, t->hi[2]);
+            }
+            lo[0] = l0; lo[1] = l1; lo[2] = l2; hi[0] = h0; hi[1] = h1; hi[2] = h2;
+        };
+        auto bounds_parallel = [&](uint32_t first, uint32_t count, float* lo, float* hi)
+        {
+            float l0 = 1e30f, l1 = 1e30f, l2 = 1e30f, h0 = -1e30f, h1 = -1e30f, h2 = -1e30f;
+#pragma omp parallel for schedule(static) reduction(min : l0, l1, l2) reduction(max : h0, h1, h2)
             for (int64_t i = 0; i < (int64_t)count; i++)
             {
-                const Centroid& t = triangles[first + i];  // per-triangle box travels with the centroid: no vertex gathers here
+                const Centroid& t = triangles[first + i];
                 l0 = std::min(l0, t.lo[0]); l1 = std::min(l1, t.lo[1]); l2 = std::min(l2, t.lo[2]);
                 h0 = std::max(h0, t.hi[0]); h1 = std::max(h1, t.hi[1]); h2 = std::max(h2, t.hi[2]);
             }
@@ -92,7 +104,7 @@ namespace RayTracing
         };
 
         Temp root{}; root.first = 0; root.count = (uint32_t)n; root.left = 0;
-        bounds_of(0, (uint32_t)n, root.lo, root.hi, n > kBigNode);
+        if (n > kBigNode) bounds_parallel(0, (uint32_t)n, root.lo, root.hi); else bounds_serial(0, (uint32_t)n, root.lo, root.hi);
         temp.push_back(root);
         std::vector<uint32_t> frontier{ 0 }, next, left_counts;
         std::vector<uint32_t> subtree_roots;
@@ -123,12 +135,12 @@ namespace RayTracing
             }
             // (3) bounds of the new nodes: big ones one at a time with an inner-parallel reduction, the rest in parallel
             for (uint32_t id : next)
-                if (temp[id].count > kBigNode) bounds_of(temp[id].first, temp[id].count, temp[id].lo, temp[id].hi, true);
+                if (temp[id].count > kBigNode) bounds_parallel(temp[id].first, temp[id].count, temp[id].lo, temp[id].hi);
 #pragma omp parallel for schedule(dynamic, 64) if (next.size() > 64)
             for (int64_t k = 0; k < (int64_t)next.size(); k++)
             {
                 Temp& t = temp[next[k]];
-                if (t.count <= kBigNode) bounds_of(t.first, t.count, t.lo, t.hi, false);
+                if (t.count <= kBigNode) bounds_serial(t.first, t.count, t.lo, t.hi);
             }
             frontier.swap(next);
         }
@@ -136,9 +148,24 @@ namespace RayTracing
         lap("top tree");
         // phase 2: depth-first subtrees, one thread each. local[0] is the subtree root, local[1..] its descendants in the
         // reference's order relative to the root's block; child links are local indices.
-        std::vector<std::vector<RtBVHNode>> local(subtree_roots.size());
+        // Blocks live in per-thread chunked arenas (one allocation per ~32 MB, not per subtree: concurrent large malloc/free
+        // pairs serialise on the process's address-space lock).
+        struct Block { const RtBVHNode* nodes = nullptr; uint32_t size = 0; };
+        std::vector<Block> local(subtree_roots.size());
+        int arena_count = 1;
+#ifdef _OPENMP
+        arena_count = omp_get_max_threads();
+#endif
+        std::vector<std::vector<std::unique_ptr<RtBVHNode[]>>> arenas(arena_count);
+        constexpr size_t kChunkNodes = 1u << 20;
 #pragma omp parallel if (subtree_roots.size() > 1)
         {
+            int me = 0;
+#ifdef _OPENMP
+            me = omp_get_thread_num();
+#endif
+            auto& chunks = arenas[me];
+            size_t chunk_used = kChunkNodes;
             std::vector<RtBVHNode> scratch; std::vector<uint32_t> work;
 #pragma omp for schedule(dynamic, 1)
             for (int64_t s = 0; s < (int64_t)subtree_roots.size(); s++)
@@ -158,16 +185,25 @@ namespace RayTracing
                     if (!left_count) continue;
                     const uint32_t left = used++, right = used++;
                     float lo[3], hi[3];
-                    bounds_of(t.first, left_count, lo, hi, false);
+                    bounds_serial(t.first, left_count, lo, hi);
                     scratch[left].bounds_min = RtVec3{ lo[0], lo[1], lo[2] }; scratch[left].bounds_max = RtVec3{ hi[0], hi[1], hi[2] };
                     scratch[left].first_index = t.first; scratch[left].prim_count = left_count;
-                    bounds_of(t.first + left_count, t.count - left_count, lo, hi, false);
+                    bounds_serial(t.first + left_count, t.count - left_count, lo, hi);
                     scratch[right].bounds_min = RtVec3{ lo[0], lo[1], lo[2] }; scratch[right].bounds_max = RtVec3{ hi[0], hi[1], hi[2] };
                     scratch[right].first_index = t.first + left_count; scratch[right].prim_count = t.count - left_count;
                     node.first_index = left; node.prim_count = 0;
                     work.push_back(right); work.push_back(left);
                 }
-                local[s].assign(scratch.begin(), scratch.begin() + used);
+                RtBVHNode* dst;
+                if (used > kChunkNodes) { chunks.emplace_back(new RtBVHNode[used]); dst = chunks.back().get(); chunk_used = kChunkNodes; }
+                else
+                {
+                    if (chunk_used + used > kChunkNodes) { chunks.emplace_back(new RtBVHNode[kChunkNodes]); chunk_used = 0; }
+                    dst = chunks.back().get() + chunk_used;
+                    chunk_used += used;
+                }
+                std::copy(scratch.begin(), scratch.begin() + used, dst);
+                local[s] = Block{ dst, used };
             }
         }
 
@@ -175,7 +211,7 @@ namespace RayTracing
         // phase 3: reference numbering from subtree sizes
         const size_t total = temp.size();
         std::vector<uint32_t> desc(total, 0), final_index(total, 0), block_base(total, 0);
-        for (size_t s = 0; s < subtree_roots.size(); s++) desc[subtree_roots[s]] = (uint32_t)local[s].size() - 1;
+        for (size_t s = 0; s < subtree_roots.size(); s++) desc[subtree_roots[s]] = local[s].size - 1;
         for (size_t t = total; t-- > 0;)
             if (temp[t].left) desc[t] = 2 + desc[temp[t].left] + desc[temp[t].left + 1];
         final_index[0] = 0; block_base[0] = 1;
@@ -201,14 +237,13 @@ namespace RayTracing
         for (int64_t s = 0; s < (int64_t)subtree_roots.size(); s++)
         {
             const uint32_t t = subtree_roots[s], base = block_base[t];  // local i >= 1 -> base + i - 1
-            const std::vector<RtBVHNode>& src = local[s];
-            for (size_t i = 0; i < src.size(); i++)
+            const Block& src = local[s];
+            for (size_t i = 0; i < src.size; i++)
             {
-                RtBVHNode out = src[i];
+                RtBVHNode out = src.nodes[i];
                 if (out.prim_count == 0) out.first_index = base + out.first_index - 1;
                 nodes[i ? base + (uint32_t)i - 1 : final_index[t]] = out;
             }
-            std::vector<RtBVHNode>().swap(local[s]);
         }
         lap("numbering + copy");
         face_indices.resize(n);

@@ -22,7 +22,6 @@ namespace RayTracing
 
     private:
         struct Centroid { float c[3]; uint32_t index; float lo[3], hi[3]; };  // centroid, face id, the triangle's own box
-        void UpdateBounds(uint32_t node_index);
 
         std::vector<RtBVHNode> nodes;
         std::vector<Centroid> triangles;

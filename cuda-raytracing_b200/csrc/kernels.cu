@@ -91,9 +91,13 @@ template <int kVariant>
 __device__ __forceinline__ void closest_hit(const AccelView& A, const SceneView& S, bool with_spheres, Vec3 o, Vec3 d, HitRecord& h)
 {
     const Vec3 nd = normalize3(d);
-    h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
-    if (with_spheres) sphere_tests(S.spheres, S.sphere_count, o, nd, h);
-    if (kVariant == 0 && dot3(d, d) >= RT_SHORT_DIR2) trace_wide<true>(A, o, d, nd, h);
+    auto reinit = [&](HitRecord& r)
+    {
+        r.t = 1e30f; r.id = RT_MISS_ID; r.slot = 0; r.key = RT_MISS_ID; r.bu = 0; r.bv = 0;
+        if (with_spheres) sphere_tests(S.spheres, S.sphere_count, o, nd, r);
+    };
+    reinit(h);
+    if (kVariant == 0 && dot3(d, d) >= RT_SHORT_DIR2) trace_wide<true>(A, o, d, nd, h, reinit);
     else trace_reference_order<true>(A, o, d, nd, h);
 }
 

@@ -91,9 +91,13 @@ __global__ void __launch_bounds__(256, kMinBlocks) pathtrace_megakernel(AccelVie
                 bounce = 0; fresh = false;
             }
             const Vec3 nd = normalize3(ps.d);
-            HitRecord h; h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
-            sphere_tests(S.spheres, S.sphere_count, ps.o, nd, h);
-            if (kMode == 0) trace_wide<false, true>(A, ps.o, ps.d, nd, h);
+            auto reinit = [&](HitRecord& r)
+            {
+                r.t = 1e30f; r.id = RT_MISS_ID; r.slot = 0; r.key = RT_MISS_ID; r.bu = 0; r.bv = 0;
+                sphere_tests(S.spheres, S.sphere_count, ps.o, nd, r);
+            };
+            HitRecord h; reinit(h);
+            if (kMode == 0) trace_wide<false, true>(A, ps.o, ps.d, nd, h, reinit);
             else trace_reference_order<false>(A, ps.o, ps.d, nd, h, &work_nodes, &work_tris);
             rays++;
             bool alive;
@@ -166,9 +170,13 @@ __global__ void __launch_bounds__(256) ambient_occlusion_kernel(AccelView A, Sce
         for (int k = 0; k <= ao_rays; k++)
         {
             const Vec3 nd = normalize3(d);
-            HitRecord h; h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
-            sphere_tests(S.spheres, S.sphere_count, o, nd, h);
-            trace_wide<false, true>(A, o, d, nd, h);
+            auto reinit = [&](HitRecord& r)
+            {
+                r.t = 1e30f; r.id = RT_MISS_ID; r.slot = 0; r.key = RT_MISS_ID; r.bu = 0; r.bv = 0;
+                sphere_tests(S.spheres, S.sphere_count, o, nd, r);
+            };
+            HitRecord h; reinit(h);
+            trace_wide<false, true>(A, o, d, nd, h, reinit);
             rays++;
             if (k == 0)
             {

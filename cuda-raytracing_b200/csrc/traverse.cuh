@@ -146,12 +146,26 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
 #ifndef RT_TW_FOLD
 #define RT_TW_FOLD 1
 #endif
+#ifndef RT_TW_NODES
+#define RT_TW_NODES 2
+#endif
+#ifndef RT_TW_BATCH
+#define RT_TW_BATCH 8
+#endif
+#ifndef RT_TW_DEFER
+#define RT_TW_DEFER 1
+#endif
 #ifndef RT_TW_MODE
 #define RT_TW_MODE 3
 #endif
 
-template <bool kTieById, bool kFma = false>
-__device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, Vec3 nd, HitRecord& h)
+//   kDeferred (template): the exact reference-leaf box re-check (6 IEEE divisions, ~110 instructions, executed by the ~2 lanes
+//     that just accepted a candidate: 12 % of the megakernel's issue slots) is not done per accepted candidate but ONCE, on the
+//     winner, after the loop. Unverified candidates only ever shrink the search interval, so any candidate that beats them is
+//     still found; if the WINNER's leaf box fails (a ray grazing a leaf box within rounding - rare) the function returns false
+//     and the caller redoes the ray with the per-candidate check (trace_wide below). Exact by construction.
+template <bool kTieById, bool kFma, bool kDeferred>
+__device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3 d, Vec3 nd, HitRecord& h)
 {
     const float start_length = h.t;
     // reciprocal of the normalised direction; zero components -> huge finite (conservative)
@@ -226,7 +240,7 @@ __device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, V
         else if (hit1) node = ch.y;                                                                                         \
         else RT_POP();                                                                                                      \
     } while (0)
-#define RT_LEAF_STEP(ref) leaf_tests<true, kTieById>(A, (ref) & 0x07FFFFFFu, (((ref) >> 27) & 0xFu) + 1u, o, d, nd, start_length, h, verified_ptr)
+#define RT_LEAF_STEP(ref) leaf_tests<!kDeferred, kTieById>(A, (ref) & 0x07FFFFFFu, (((ref) >> 27) & 0xFu) + 1u, o, d, nd, start_length, h, verified_ptr)
 
 #if RT_TW_MODE == 1
     // if-if: one node of either kind per iteration, no inner loop to wait in
@@ -242,7 +256,44 @@ __device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, V
         if (!(node & RT_LEAF_BIT)) RT_NODE_STEP();
         else
         {
-            leaf_tests<true, kTieById>(A, node & 0x07FFFFFFu, 1u, o, d, nd, start_length, h, verified_ptr);
+            leaf_tests<!kDeferred, kTieById>(A, node & 0x07FFFFFFu, 1u, o, d, nd, start_length, h, verified_ptr);
+            if (node & 0x78000000u) node = node - (1u << 27) + 1u;
+            else RT_POP();
+        }
+    }
+#elif RT_TW_MODE == 4
+    // mode 3 + warp vote: lanes that sit on a leaf wait until RT_TW_BATCH of them do (or nobody has an inner node left), so the
+    // triangle code runs with more lanes. All lanes that entered together stay in the loop until the last one is done.
+    {
+        const unsigned entry = __activemask();
+        for (;;)
+        {
+            const bool inner = !(node & RT_LEAF_BIT);                       // (the sentinel has the leaf bit set)
+            const bool leaf = (node & RT_LEAF_BIT) && node != RT_SENTINEL;
+            const unsigned m_inner = __ballot_sync(entry, inner), m_leaf = __ballot_sync(entry, leaf);
+            if ((m_inner | m_leaf) == 0u) break;
+            if (inner) RT_NODE_STEP();
+            if (leaf && (__popc(m_leaf) >= RT_TW_BATCH || m_inner == 0u))
+            {
+                leaf_tests<!kDeferred, kTieById>(A, node & 0x07FFFFFFu, 1u, o, d, nd, start_length, h, verified_ptr);
+                if (node & 0x78000000u) node = node - (1u << 27) + 1u;
+                else RT_POP();
+            }
+        }
+    }
+#elif RT_TW_MODE == 6
+    // if-if, up to RT_TW_NODES wide nodes then one triangle per iteration (amortises the serialised triangle path)
+    while (node != RT_SENTINEL)
+    {
+        if (!(node & RT_LEAF_BIT))
+        {
+            RT_NODE_STEP();
+#pragma unroll
+            for (int k = 1; k < RT_TW_NODES; k++) if (!(node & RT_LEAF_BIT)) RT_NODE_STEP();
+        }
+        else
+        {
+            leaf_tests<!kDeferred, kTieById>(A, node & 0x07FFFFFFu, 1u, o, d, nd, start_length, h, verified_ptr);
             if (node & 0x78000000u) node = node - (1u << 27) + 1u;
             else RT_POP();
         }
@@ -291,6 +342,34 @@ __device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, V
 #undef RT_SLAB
 #undef RT_PUSH
 #undef RT_POP
+    if (kDeferred && h.id != RT_MISS_ID && !(h.id & RT_SPHERE_ID_BIT))
+    {   // h entered as a sphere hit or a miss, so a triangle id means "found here": verify its reference leaf (main_raytracing.cu:46)
+        const uint32_t leaf = __ldg(&A.tris[h.slot].ref_leaf);
+#ifdef RT_TW_FORCE_REDO
+        if ((h.slot & RT_TW_FORCE_REDO) == 0u) return false;  // test hook: exercise the redo path on a fraction of the rays
+#endif
+        return exact_box(o, d, A.ref_nodes + leaf, start_length);
+    }
+    return true;
+}
+
+template <bool kTieById, bool kFma>
+__device__ __noinline__ void trace_wide_checked(const AccelView& A, Vec3 o, Vec3 d, Vec3 nd, HitRecord& h)
+{
+    trace_wide_impl<kTieById, kFma, false>(A, o, d, nd, h);
+}
+
+// `h` enters holding what reinit(h) produces (a miss, or the sphere result); reinit is only called again on the rare redo.
+template <bool kTieById, bool kFma = false, class Reinit>
+__device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, Vec3 nd, HitRecord& h, Reinit reinit)
+{
+#if RT_TW_DEFER
+    if (trace_wide_impl<kTieById, kFma, true>(A, o, d, nd, h)) return;
+    reinit(h);
+    trace_wide_checked<kTieById, kFma>(A, o, d, nd, h);
+#else
+    trace_wide_impl<kTieById, kFma, false>(A, o, d, nd, h);
+#endif
 }
 
 // Reference-order traversal over the reference-layout nodes: right child first, exact box test at

@@ -98,9 +98,11 @@ class CpuReference:
         rate = rays / max(s, 1e-6)
         rays_per_row_spp = rays / (self.a.height / 32.0)
         want = rate * target_seconds
-        stride = 8
-        spp = int(max(1, min(self.a.spp, round(want / (rays_per_row_spp * self.a.height / stride)))))
-        return stride, spp
+        for stride in (8, 4, 2, 1):  # densest row sampling whose sample count still fits the workload's spp
+            spp = int(round(want / (rays_per_row_spp * self.a.height / stride)))
+            if spp <= self.a.spp:
+                break
+        return stride, int(max(1, min(self.a.spp, spp)))
 
     def sample_desc(self, stride, spp):
         a = self.a
@@ -326,7 +328,7 @@ def run_b200_arm(a):
     if world == 1 and not a.no_cpu_baseline:
         try:
             cpu = CpuReference(a)
-            stride, spp = cpu.calibrate(2.5)
+            stride, spp = cpu.calibrate(12.0)  # ~10-30 s of CPU work (all host threads)
             s, r, threads = cpu.run(stride, spp)
             line["cpu_baseline"] = {"value": r / s / 1e6, "unit": UNIT, "cores": threads, "kind": "reference", "sample": cpu.sample_desc(stride, spp),
                                     "seconds": s}

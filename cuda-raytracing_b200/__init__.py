@@ -115,6 +115,8 @@ SYMBOLS = {
     "rt_host_tracer_frame_index": (_I, [_P]),
     "rt_host_tracer_set_sampling": (_I, [_P, _I, _I, _I]),
     "rt_host_tracer_ray_count": (C.c_ulonglong, [_P]),
+    "rt_host_tracer_save_checkpoint": (_I, [_P, C.c_char_p]),
+    "rt_host_tracer_load_checkpoint": (_I, [_P, C.c_char_p]),
     "rt_host_write_ppm": (_I, [C.c_char_p, _P, _I, _I]),
 }
 

@@ -1,6 +1,7 @@
 """Thin Python handles over the host C wrapper (include/b200rt_host.h). Names follow the reference's
 classes (Scene / Camera / CUDARayTracer, RayTracing/Scene.h, RayTracing/RayTracing.h)."""
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -181,6 +182,13 @@ class Tracer:
         n = C.c_uint64()
         check(lib().rt_host_tracer_render_to_host(self.handle, frames, ptr(host_pixels), host_pitch, C.byref(n)))
         return n.value
+
+    def save_checkpoint(self, path):
+        """{frame index, both surfaces, RNG states} -> file (CUDARayTracer::SaveCheckpoint)."""
+        check(lib().rt_host_tracer_save_checkpoint(self.handle, os.fsencode(path)))
+
+    def load_checkpoint(self, path):
+        check(lib().rt_host_tracer_load_checkpoint(self.handle, os.fsencode(path)))
 
     def on_resize(self, surface, last_frame_surface, width, height, pitch):
         self._keep = (surface, last_frame_surface)

@@ -31,9 +31,11 @@ struct RtFloat4 { float x, y, z, w; };
 
 struct alignas(64) WideNode
 {
-    RtFloat4 a;   // lo0.x lo0.y lo0.z hi0.x
-    RtFloat4 b;   // hi0.y hi0.z lo1.x lo1.y
-    RtFloat4 c;   // lo1.z hi1.x hi1.y hi1.z
+    // register-pair friendly order for Blackwell's packed fp32 ops (add/mul/fma .f32x2): every aligned pair of a 128-bit load
+    // is combined with one per-ray constant pair, (x, y) or (z, z)
+    RtFloat4 a;   // lo0.x lo0.y | hi0.x hi0.y
+    RtFloat4 b;   // lo1.x lo1.y | hi1.x hi1.y
+    RtFloat4 c;   // lo0.z hi0.z | lo1.z hi1.z
     uint32_t child[2];
     uint32_t pad[2];
 };

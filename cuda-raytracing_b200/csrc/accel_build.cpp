@@ -36,8 +36,8 @@ namespace
 
     inline void SetChildBox(WideNode& w, int which, const Box& b)
     {
-        if (which == 0) { w.a = { b.lo[0], b.lo[1], b.lo[2], b.hi[0] }; w.b.x = b.hi[1]; w.b.y = b.hi[2]; }
-        else { w.b.z = b.lo[0]; w.b.w = b.lo[1]; w.c = { b.lo[2], b.hi[0], b.hi[1], b.hi[2] }; }
+        if (which == 0) { w.a = { b.lo[0], b.lo[1], b.hi[0], b.hi[1] }; w.c.x = b.lo[2]; w.c.y = b.hi[2]; }
+        else { w.b = { b.lo[0], b.lo[1], b.hi[0], b.hi[1] }; w.c.z = b.lo[2]; w.c.w = b.hi[2]; }
     }
 
     struct Builder

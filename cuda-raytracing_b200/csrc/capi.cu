@@ -89,7 +89,7 @@ int rt_accel_create(const RtBVHNode* nodes, uint32_t node_count, const uint32_t*
     const size_t bw = host.wide.size() * sizeof(WideNode), bt = host.tris.size() * sizeof(TriRecord);
     const size_t bs = host.shade.size() * sizeof(ShadeRecord), br = (size_t)node_count * sizeof(RtBVHNode);
     cudaError_t e = cudaMalloc(&d_wide, bw);
-    if (e == cudaSuccess) e = cudaMalloc(&d_tris, bt);
+    if (e == cudaSuccess) e = cudaMalloc(&d_tris, bt + 64);  // + pad: the unified fetch of trace_wide reads 56 B from the last record
     if (e == cudaSuccess) e = cudaMalloc(&d_shade, bs);
     if (e == cudaSuccess) e = cudaMalloc(&d_ref, br);
     if (e == cudaSuccess) e = cudaMemcpy(d_wide, host.wide.data(), bw, cudaMemcpyHostToDevice);

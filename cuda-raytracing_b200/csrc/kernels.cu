@@ -249,17 +249,17 @@ __device__ __forceinline__ void extend_inner(const AccelView& A, ExtendLane& L, 
     const WideNode* w = A.wide + L.node;
     const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32);
     const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
-    float t1 = fmaf(a.x, L.ix, L.cx), t2 = fmaf(a.w, L.ix, L.cx);
+    float t1 = fmaf(a.x, L.ix, L.cx), t2 = fmaf(a.z, L.ix, L.cx);
     float mn0 = fminf(t1, t2), mx0 = fmaxf(t1, t2);
-    t1 = fmaf(a.y, L.iy, L.cy); t2 = fmaf(b.x, L.iy, L.cy);
+    t1 = fmaf(a.y, L.iy, L.cy); t2 = fmaf(a.w, L.iy, L.cy);
     float mnb = fminf(t1, t2), mxb = fmaxf(t1, t2);
-    t1 = fmaf(a.z, L.iz, L.cz); t2 = fmaf(b.y, L.iz, L.cz);
+    t1 = fmaf(c.x, L.iz, L.cz); t2 = fmaf(c.y, L.iz, L.cz);
     mn0 = fmaxf(fmaxf(mn0, mnb), fminf(t1, t2)); mx0 = fminf(fminf(mx0, mxb), fmaxf(t1, t2));
-    t1 = fmaf(b.z, L.ix, L.cx); t2 = fmaf(c.y, L.ix, L.cx);
+    t1 = fmaf(b.x, L.ix, L.cx); t2 = fmaf(b.z, L.ix, L.cx);
     float mn1 = fminf(t1, t2), mx1 = fmaxf(t1, t2);
-    t1 = fmaf(b.w, L.iy, L.cy); t2 = fmaf(c.z, L.iy, L.cy);
+    t1 = fmaf(b.y, L.iy, L.cy); t2 = fmaf(b.w, L.iy, L.cy);
     mnb = fminf(t1, t2); mxb = fmaxf(t1, t2);
-    t1 = fmaf(c.x, L.iz, L.cz); t2 = fmaf(c.w, L.iz, L.cz);
+    t1 = fmaf(c.z, L.iz, L.cz); t2 = fmaf(c.w, L.iz, L.cz);
     mn1 = fmaxf(fmaxf(mn1, mnb), fminf(t1, t2)); mx1 = fminf(fminf(mx1, mxb), fmaxf(t1, t2));
     const float lo0 = fmaf(-kWiden, fabsf(mn0), mn0) - L.slack, hi0 = fmaf(kWiden, fabsf(mx0), mx0) + L.slack;
     const float lo1 = fmaf(-kWiden, fabsf(mn1), mn1) - L.slack, hi1 = fmaf(kWiden, fabsf(mx1), mx1) + L.slack;

@@ -12,6 +12,10 @@
 #include <cstdlib>
 #include "shade.cuh"
 
+#ifndef RT_PT_FMA
+#define RT_PT_FMA 0  // 1: slab test of the path tracer in FMA form (traverse.cuh, kFma): 1 % faster on the bunny, 1.9x slower on config 4b
+#endif
+
 __device__ __forceinline__ void camera_ray_pt(const RtCamera& cam, float u, float v, Vec3& o, Vec3& d)
 {
     o = mk3(cam.origin.x, cam.origin.y, cam.origin.z);
@@ -97,7 +101,7 @@ __global__ void __launch_bounds__(256, kMinBlocks) pathtrace_megakernel(AccelVie
                 sphere_tests(S.spheres, S.sphere_count, ps.o, nd, r);
             };
             HitRecord h; reinit(h);
-            if (kMode == 0) trace_wide<false, true>(A, ps.o, ps.d, nd, h, reinit);
+            if (kMode == 0) trace_wide<false, RT_PT_FMA != 0>(A, ps.o, ps.d, nd, h, reinit);
             else trace_reference_order<false>(A, ps.o, ps.d, nd, h, &work_nodes, &work_tris);
             rays++;
             bool alive;
@@ -140,6 +144,7 @@ cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, cons
     static int min_blocks = 0;
     if (!min_blocks) { const char* v = getenv("B200RT_MINBLOCKS"); min_blocks = v ? atoi(v) : 5; }  // occupancy sweep hook (profiles/)
     if (p.variant == 2) pathtrace_megakernel<2, 3><<<grid, block, 0, stream>>>(accel, scene, P);
+    else if (min_blocks == 6) pathtrace_megakernel<0, 6><<<grid, block, 0, stream>>>(accel, scene, P);
     else if (min_blocks == 4) pathtrace_megakernel<0, 4><<<grid, block, 0, stream>>>(accel, scene, P);
     else if (min_blocks == 3) pathtrace_megakernel<0, 3><<<grid, block, 0, stream>>>(accel, scene, P);
     else if (min_blocks == 2) pathtrace_megakernel<0, 2><<<grid, block, 0, stream>>>(accel, scene, P);
@@ -176,7 +181,7 @@ __global__ void __launch_bounds__(256) ambient_occlusion_kernel(AccelView A, Sce
                 sphere_tests(S.spheres, S.sphere_count, o, nd, r);
             };
             HitRecord h; reinit(h);
-            trace_wide<false, true>(A, o, d, nd, h, reinit);
+            trace_wide<false, RT_PT_FMA != 0>(A, o, d, nd, h, reinit);
             rays++;
             if (k == 0)
             {

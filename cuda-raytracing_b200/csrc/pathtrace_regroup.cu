@@ -177,17 +177,17 @@ __global__ void __launch_bounds__(256, kMinBlocks) pathtrace_regroup_kernel(Acce
                 const WideNode* w = A.wide + node;
                 const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32);
                 const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
-                float t1 = fmaf(a.x, ix, cx), t2 = fmaf(a.w, ix, cx);
+                float t1 = fmaf(a.x, ix, cx), t2 = fmaf(a.z, ix, cx);
                 float mn0 = fminf(t1, t2), mx0 = fmaxf(t1, t2);
-                t1 = fmaf(a.y, iy, cy); t2 = fmaf(b.x, iy, cy);
+                t1 = fmaf(a.y, iy, cy); t2 = fmaf(a.w, iy, cy);
                 float mnb = fminf(t1, t2), mxb = fmaxf(t1, t2);
-                t1 = fmaf(a.z, iz, cz); t2 = fmaf(b.y, iz, cz);
+                t1 = fmaf(c.x, iz, cz); t2 = fmaf(c.y, iz, cz);
                 mn0 = fmaxf(fmaxf(mn0, mnb), fminf(t1, t2)); mx0 = fminf(fminf(mx0, mxb), fmaxf(t1, t2));
-                t1 = fmaf(b.z, ix, cx); t2 = fmaf(c.y, ix, cx);
+                t1 = fmaf(b.x, ix, cx); t2 = fmaf(b.z, ix, cx);
                 float mn1 = fminf(t1, t2), mx1 = fmaxf(t1, t2);
-                t1 = fmaf(b.w, iy, cy); t2 = fmaf(c.z, iy, cy);
+                t1 = fmaf(b.y, iy, cy); t2 = fmaf(b.w, iy, cy);
                 mnb = fminf(t1, t2); mxb = fmaxf(t1, t2);
-                t1 = fmaf(c.x, iz, cz); t2 = fmaf(c.w, iz, cz);
+                t1 = fmaf(c.z, iz, cz); t2 = fmaf(c.w, iz, cz);
                 mn1 = fmaxf(fmaxf(mn1, mnb), fminf(t1, t2)); mx1 = fminf(fminf(mx1, mxb), fmaxf(t1, t2));
                 // folded conservative cull (traverse.cuh, RT_TW_FOLD): max(entry, 0) <= widen(min(exit, best))
                 const bool hit0 = fmaxf(mn0, 0.0f) <= fmaf(fminf(mx0, h.t), kFoldK1, k2);

@@ -101,6 +101,29 @@ __device__ __forceinline__ bool accept(float t, uint32_t key, const HitRecord& h
     return t < h.t || (key < h.key && !(h.id & RT_SPHERE_ID_BIT));  // a sphere at the same t keeps the hit (:62, `>=`)
 }
 
+// One triangle record (already loaded) against the ray: glm test, tie rule, optional per-candidate exact leaf-box check.
+template <bool kLazyExactBox, bool kTieById>
+__device__ __forceinline__ void leaf_test_one(const AccelView& A, float4 r0, float4 r1, float4 r2, uint32_t slot, Vec3 o, Vec3 d, Vec3 nd,
+                                              float start_length, HitRecord& h, uint32_t* verified_leaf = nullptr)
+{
+    float t, bu, bv;
+    if (!tri_test(o, nd, r0, r1, r2, t, bu, bv)) return;
+    const uint32_t id = __float_as_uint(r0.w);
+    const uint32_t key = kTieById ? id : __float_as_uint(r2.w);
+    if (!accept(t, key, h)) return;
+    if (kLazyExactBox)
+    {   // the reference only tests this triangle if its leaf's box passes (main_raytracing.cu:46); optional one-entry cache of
+        // the last leaf that passed (the smooth/flat duplicates of a face share a leaf and are accepted back to back)
+        const uint32_t leaf = __float_as_uint(r1.w);
+        if (!verified_leaf || *verified_leaf != leaf)
+        {
+            if (!exact_box(o, d, A.ref_nodes + leaf, start_length)) return;
+            if (verified_leaf) *verified_leaf = leaf;
+        }
+    }
+    h.t = t; h.id = id; h.slot = slot; h.key = key; h.bu = bu; h.bv = bv;
+}
+
 template <bool kLazyExactBox, bool kTieById>
 __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, uint32_t count, Vec3 o, Vec3 d, Vec3 nd,
                                            float start_length, HitRecord& h, uint32_t* verified_leaf = nullptr)
@@ -109,22 +132,7 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
     for (uint32_t i = 0; i < count; i++)
     {
         const float4 r0 = ldg4(&tr[i]), r1 = ldg4(reinterpret_cast<const char*>(&tr[i]) + 16), r2 = ldg4(reinterpret_cast<const char*>(&tr[i]) + 32);
-        float t, bu, bv;
-        if (!tri_test(o, nd, r0, r1, r2, t, bu, bv)) continue;
-        const uint32_t id = __float_as_uint(r0.w);
-        const uint32_t key = kTieById ? id : __float_as_uint(r2.w);
-        if (!accept(t, key, h)) continue;
-        if (kLazyExactBox)
-        {   // the reference only tests this triangle if its leaf's box passes (main_raytracing.cu:46); optional one-entry cache of
-            // the last leaf that passed (the smooth/flat duplicates of a face share a leaf and are accepted back to back)
-            const uint32_t leaf = __float_as_uint(r1.w);
-            if (!verified_leaf || *verified_leaf != leaf)
-            {
-                if (!exact_box(o, d, A.ref_nodes + leaf, start_length)) continue;
-                if (verified_leaf) *verified_leaf = leaf;
-            }
-        }
-        h.t = t; h.id = id; h.slot = first + i; h.key = key; h.bu = bu; h.bv = bv;
+        leaf_test_one<kLazyExactBox, kTieById>(A, r0, r1, r2, first + i, o, d, nd, start_length, h, verified_leaf);
     }
 }
 
@@ -146,6 +154,15 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
 #ifndef RT_TW_FOLD
 #define RT_TW_FOLD 1
 #endif
+#ifndef RT_TW_PACKED
+#define RT_TW_PACKED 1
+#endif
+#ifndef RT_TW_AXIS_SLACK
+#define RT_TW_AXIS_SLACK 0
+#endif
+#ifndef RT_TW_PREFETCH
+#define RT_TW_PREFETCH 0
+#endif
 #ifndef RT_TW_NODES
 #define RT_TW_NODES 2
 #endif
@@ -156,7 +173,7 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
 #define RT_TW_DEFER 1
 #endif
 #ifndef RT_TW_MODE
-#define RT_TW_MODE 3
+#define RT_TW_MODE 7
 #endif
 
 //   kDeferred (template): the exact reference-leaf box re-check (6 IEEE divisions, ~110 instructions, executed by the ~2 lanes
@@ -200,25 +217,82 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
     // k1 = (1 + kWiden) / (1 - kWiden) and k2 = 2 slack / (1 - kWiden), both rounded up, move the whole widening onto the exit side,
     // so the entry side needs none (a superset of the two-sided form term by term; -6 instructions per wide node).
     const float k1 = 1.0f + 2.5e-6f, k2 = 2.1f * slack;
+    // RT_TW_AXIS_SLACK (kFma only): the absolute error of fma(plane, inv, -(o*inv)) is ~ulp(|o*inv|) of THAT axis, and |o*inv| is
+    // huge exactly on the axes the ray is nearly perpendicular to. One slack = the max over the axes (above) makes every entry/exit
+    // that wrong: on the 13.9 M-triangle grid (coordinates ~300, many near-axis-parallel rays) it is larger than the leaves and the
+    // cull against the current best stops working (path trace 23.6 ms vs 14.5 ms with the exact (plane - o) * inv form). Here each
+    // axis carries its own slack inside its fma constant: entry planes use c - eps, exit planes c + eps. Which plane is the entry
+    // one follows from the sign of inv (fma is monotonic in the plane), so the min/max pairs become selects: same instruction count.
+    const float2 i_xy = make_float2(ix, iy), i_zz = make_float2(iz, iz), no_xy = make_float2(-o.x, -o.y), no_zz = make_float2(-o.z, -o.z);
+    const float2 c_xy = make_float2(cx, cy), c_zz = make_float2(cz, cz);
+    const bool neg_x = ix < 0.0f, neg_y = iy < 0.0f, neg_z = iz < 0.0f;
+    const float ex = 4.0e-7f * fabsf(ax) + 1e-30f, ey = 4.0e-7f * fabsf(ay) + 1e-30f, ez = 4.0e-7f * fabsf(az) + 1e-30f;
+    const float cnx = cx - ex, cny = cy - ey, cnz = cz - ez, cfx = cx + ex, cfy = cy + ey, cfz = cz + ez;
 #define RT_NODE_STEP()                                                                                                     \
     do {                                                                                                                    \
         const WideNode* w = A.wide + node;                                                                                  \
         const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32); \
         const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));                      \
-        float t1 = RT_SLAB(a.x, ix, cx, o.x), t2 = RT_SLAB(a.w, ix, cx, o.x);                                               \
-        float mn0 = fminf(t1, t2), mx0 = fmaxf(t1, t2);                                                                     \
-        t1 = RT_SLAB(a.y, iy, cy, o.y); t2 = RT_SLAB(b.x, iy, cy, o.y);                                                     \
-        mn0 = fmaxf(mn0, fminf(t1, t2)); mx0 = fminf(mx0, fmaxf(t1, t2));                                                   \
-        t1 = RT_SLAB(a.z, iz, cz, o.z); t2 = RT_SLAB(b.y, iz, cz, o.z);                                                     \
-        mn0 = fmaxf(mn0, fminf(t1, t2)); mx0 = fminf(mx0, fmaxf(t1, t2));                                                   \
-        t1 = RT_SLAB(b.z, ix, cx, o.x); t2 = RT_SLAB(c.y, ix, cx, o.x);                                                     \
-        float mn1 = fminf(t1, t2), mx1 = fmaxf(t1, t2);                                                                     \
-        t1 = RT_SLAB(b.w, iy, cy, o.y); t2 = RT_SLAB(c.z, iy, cy, o.y);                                                     \
-        mn1 = fmaxf(mn1, fminf(t1, t2)); mx1 = fminf(mx1, fmaxf(t1, t2));                                                   \
-        t1 = RT_SLAB(c.x, iz, cz, o.z); t2 = RT_SLAB(c.w, iz, cz, o.z);                                                     \
-        mn1 = fmaxf(mn1, fminf(t1, t2)); mx1 = fminf(mx1, fmaxf(t1, t2));                                                   \
+        RT_NODE_MATH(a, b, c, ch);                                                                                          \
+    } while (0)
+#define RT_NODE_MATH(a, b, c, ch)                                                                                          \
+    do {                                                                                                                    \
+        if (kFma && RT_TW_AXIS_SLACK)                                                                                       \
+        {                                                                                                                   \
+            const float en0 = fmaxf(fmaxf(fmaf(neg_x ? a.z : a.x, ix, cnx), fmaf(neg_y ? a.w : a.y, iy, cny)), fmaf(neg_z ? c.y : c.x, iz, cnz)); \
+            const float ex0 = fminf(fminf(fmaf(neg_x ? a.x : a.z, ix, cfx), fmaf(neg_y ? a.y : a.w, iy, cfy)), fmaf(neg_z ? c.x : c.y, iz, cfz)); \
+            const float en1 = fmaxf(fmaxf(fmaf(neg_x ? b.z : b.x, ix, cnx), fmaf(neg_y ? b.w : b.y, iy, cny)), fmaf(neg_z ? c.w : c.z, iz, cnz)); \
+            const float ex1 = fminf(fminf(fmaf(neg_x ? b.x : b.z, ix, cfx), fmaf(neg_y ? b.y : b.w, iy, cfy)), fmaf(neg_z ? c.z : c.w, iz, cfz)); \
+            const bool h0 = fmaxf(en0, 0.0f) <= fminf(ex0, h.t) * k1, h1 = fmaxf(en1, 0.0f) <= fminf(ex1, h.t) * k1;        \
+            if (h0 && h1)                                                                                                   \
+            {                                                                                                               \
+                const bool swap = en1 < en0;                                                                                \
+                RT_PUSH(swap ? ch.x : ch.y);                                                                                \
+                node = swap ? ch.y : ch.x;                                                                                  \
+            }                                                                                                               \
+            else if (h0) node = ch.x;                                                                                       \
+            else if (h1) node = ch.y;                                                                                       \
+            else RT_POP();                                                                                                  \
+            break;                                                                                                          \
+        }                                                                                                                   \
+        float mn0, mx0, mn1, mx1;                                                                                           \
+        if (RT_TW_PACKED)                                                                                                   \
+        {   /* Blackwell packed fp32: six 2-wide ops per slab stage instead of twelve scalar ones; same IEEE results */     \
+            float2 d0, d1, d2, d3, d4, d5;                                                                                  \
+            if (kFma)                                                                                                       \
+            {                                                                                                               \
+                d0 = __ffma2_rn(make_float2(a.x, a.y), i_xy, c_xy); d1 = __ffma2_rn(make_float2(a.z, a.w), i_xy, c_xy);     \
+                d2 = __ffma2_rn(make_float2(b.x, b.y), i_xy, c_xy); d3 = __ffma2_rn(make_float2(b.z, b.w), i_xy, c_xy);     \
+                d4 = __ffma2_rn(make_float2(c.x, c.y), i_zz, c_zz); d5 = __ffma2_rn(make_float2(c.z, c.w), i_zz, c_zz);     \
+            }                                                                                                               \
+            else                                                                                                            \
+            {                                                                                                               \
+                d0 = __fmul2_rn(__fadd2_rn(make_float2(a.x, a.y), no_xy), i_xy); d1 = __fmul2_rn(__fadd2_rn(make_float2(a.z, a.w), no_xy), i_xy);\
+                d2 = __fmul2_rn(__fadd2_rn(make_float2(b.x, b.y), no_xy), i_xy); d3 = __fmul2_rn(__fadd2_rn(make_float2(b.z, b.w), no_xy), i_xy);\
+                d4 = __fmul2_rn(__fadd2_rn(make_float2(c.x, c.y), no_zz), i_zz); d5 = __fmul2_rn(__fadd2_rn(make_float2(c.z, c.w), no_zz), i_zz);\
+            }                                                                                                               \
+            mn0 = fmaxf(fmaxf(fminf(d0.x, d1.x), fminf(d0.y, d1.y)), fminf(d4.x, d4.y));                                    \
+            mx0 = fminf(fminf(fmaxf(d0.x, d1.x), fmaxf(d0.y, d1.y)), fmaxf(d4.x, d4.y));                                    \
+            mn1 = fmaxf(fmaxf(fminf(d2.x, d3.x), fminf(d2.y, d3.y)), fminf(d5.x, d5.y));                                    \
+            mx1 = fminf(fminf(fmaxf(d2.x, d3.x), fmaxf(d2.y, d3.y)), fmaxf(d5.x, d5.y));                                    \
+        }                                                                                                                   \
+        else                                                                                                                \
+        {                                                                                                                   \
+            float t1 = RT_SLAB(a.x, ix, cx, o.x), t2 = RT_SLAB(a.z, ix, cx, o.x);                                               \
+            mn0 = fminf(t1, t2); mx0 = fmaxf(t1, t2);                                                                         \
+            t1 = RT_SLAB(a.y, iy, cy, o.y); t2 = RT_SLAB(a.w, iy, cy, o.y);                                                     \
+            mn0 = fmaxf(mn0, fminf(t1, t2)); mx0 = fminf(mx0, fmaxf(t1, t2));                                                   \
+            t1 = RT_SLAB(c.x, iz, cz, o.z); t2 = RT_SLAB(c.y, iz, cz, o.z);                                                     \
+            mn0 = fmaxf(mn0, fminf(t1, t2)); mx0 = fminf(mx0, fmaxf(t1, t2));                                                   \
+            t1 = RT_SLAB(b.x, ix, cx, o.x); t2 = RT_SLAB(b.z, ix, cx, o.x);                                                     \
+            mn1 = fminf(t1, t2); mx1 = fmaxf(t1, t2);                                                                         \
+            t1 = RT_SLAB(b.y, iy, cy, o.y); t2 = RT_SLAB(b.w, iy, cy, o.y);                                                     \
+            mn1 = fmaxf(mn1, fminf(t1, t2)); mx1 = fminf(mx1, fmaxf(t1, t2));                                                   \
+            t1 = RT_SLAB(c.z, iz, cz, o.z); t2 = RT_SLAB(c.w, iz, cz, o.z);                                                     \
+            mn1 = fmaxf(mn1, fminf(t1, t2)); mx1 = fminf(mx1, fmaxf(t1, t2));                                                   \
+        }                                                                                                                   \
         bool hit0, hit1;                                                                                                    \
-        if (RT_TW_FOLD)                                                                                                     \
+        if (RT_TW_FOLD && kFma)                                                                                             \
         {                                                                                                                   \
             hit0 = fmaxf(mn0, 0.0f) <= fmaf(fminf(mx0, h.t), k1, k2);                                                       \
             hit1 = fmaxf(mn1, 0.0f) <= fmaf(fminf(mx1, h.t), k1, k2);                                                       \
@@ -281,6 +355,32 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
             }
         }
     }
+#elif RT_TW_MODE == 7
+    // mode 3 with ONE fetch for both kinds of step: every lane loads 56 bytes from its own record (a 64-byte wide node or a
+    // 48-byte triangle record; the arrays are padded so the last triangle's +48 read stays inside) before the kinds diverge, so
+    // the memory latency of the node lanes and of the triangle lanes overlaps instead of adding up within an iteration.
+    while (node != RT_SENTINEL)
+    {
+        const bool is_leaf = (node & RT_LEAF_BIT) != 0u;
+        const uint32_t slot = node & 0x07FFFFFFu;
+        const char* rec = is_leaf ? reinterpret_cast<const char*>(A.tris + slot) : reinterpret_cast<const char*>(A.wide + node);
+        const float4 q0 = ldg4(rec), q1 = ldg4(rec + 16), q2 = ldg4(rec + 32);
+        const uint2 q3 = __ldg(reinterpret_cast<const uint2*>(rec + 48));
+#if RT_TW_PREFETCH
+        if (is_leaf && (node & 0x78000000u))
+        {   // the next record of this leaf is the next iteration's fetch: start it now (matters when the scene is not L2-resident)
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(rec + 64));
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(rec + 95));
+        }
+#endif
+        if (!is_leaf) RT_NODE_MATH(q0, q1, q2, q3);
+        else
+        {
+            leaf_test_one<!kDeferred, kTieById>(A, q0, q1, q2, slot, o, d, nd, start_length, h, verified_ptr);
+            if (node & 0x78000000u) node = node - (1u << 27) + 1u;
+            else RT_POP();
+        }
+    }
 #elif RT_TW_MODE == 6
     // if-if, up to RT_TW_NODES wide nodes then one triangle per iteration (amortises the serialised triangle path)
     while (node != RT_SENTINEL)
@@ -338,6 +438,7 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
     }
 #endif
 #undef RT_NODE_STEP
+#undef RT_NODE_MATH
 #undef RT_LEAF_STEP
 #undef RT_SLAB
 #undef RT_PUSH

@@ -1,6 +1,10 @@
 // CUDARayTracer: per-frame protocol of RayTracing/RayTracing.cpp:205-235 over the C ABI.
 #include "RayTracing.h"
+#include <algorithm>
 #include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <vector>
 #include <cuda_runtime.h>
 #include "b200rt.h"
 
@@ -76,6 +80,67 @@ namespace RayTracing
                                            (size_t)surface.height, cudaMemcpyDeviceToHost);
         if (e != cudaSuccess) throw std::runtime_error(std::string("RenderToHost: ") + cudaGetErrorString(e));
         return h2d;
+    }
+
+    namespace
+    {
+        struct CheckpointHeader
+        {
+            char magic[8];  // "B200RTCK"
+            uint32_t version, width, height, frame_index, samples_per_launch, max_bounces, rng_state_count, rng_state_bytes;
+        };
+        struct File
+        {
+            FILE* f;
+            File(const std::string& path, const char* mode) : f(std::fopen(path.c_str(), mode)) { if (!f) throw std::runtime_error("checkpoint: cannot open " + path); }
+            ~File() { if (f) std::fclose(f); }
+        };
+        uint32_t PaddedStateCount(int width, int height) { return (uint32_t)(((size_t)width * height + 127) / 128 * 128); }
+    }
+
+    void CUDARayTracer::SaveCheckpoint(const std::string& path)
+    {
+        if (!rng_state) throw std::runtime_error("checkpoint: nothing rendered yet");
+        const size_t row = (size_t)surface.width * 16, rows = (size_t)surface.height;
+        const uint32_t count = PaddedStateCount(surface.width, surface.height);
+        std::vector<unsigned char> host(std::max(row * rows, (size_t)count * sizeof(RtRngState)));
+        CheckpointHeader h{ { 'B', '2', '0', '0', 'R', 'T', 'C', 'K' }, 1u, (uint32_t)surface.width, (uint32_t)surface.height, (uint32_t)frame_index,
+                            (uint32_t)options.samples_per_launch, (uint32_t)options.max_bounces, count, (uint32_t)sizeof(RtRngState) };
+        File out(path, "wb");
+        bool ok = std::fwrite(&h, sizeof(h), 1, out.f) == 1;
+        for (void* s : { surface.surface, surface.last_frame_surface })
+        {   // cudaMemcpy2D on the legacy stream: ordered after every Process() launched so far
+            if (cudaMemcpy2D(host.data(), row, s, surface.pitch, row, rows, cudaMemcpyDeviceToHost) != cudaSuccess) throw std::runtime_error("checkpoint: surface read failed");
+            ok = ok && std::fwrite(host.data(), row, rows, out.f) == rows;
+        }
+        if (cudaMemcpy(host.data(), rng_state, (size_t)count * sizeof(RtRngState), cudaMemcpyDeviceToHost) != cudaSuccess) throw std::runtime_error("checkpoint: RNG state read failed");
+        ok = ok && std::fwrite(host.data(), sizeof(RtRngState), count, out.f) == count;
+        if (!ok) throw std::runtime_error("checkpoint: short write to " + path);
+    }
+
+    void CUDARayTracer::LoadCheckpoint(const std::string& path)
+    {
+        File in(path, "rb");
+        CheckpointHeader h{};
+        if (std::fread(&h, sizeof(h), 1, in.f) != 1 || std::memcmp(h.magic, "B200RTCK", 8) != 0 || h.version != 1u) throw std::runtime_error("checkpoint: not a checkpoint file: " + path);
+        if ((int)h.width != surface.width || (int)h.height != surface.height) throw std::runtime_error("checkpoint: surface size differs");
+        if (h.rng_state_bytes != sizeof(RtRngState) || h.rng_state_count != PaddedStateCount(surface.width, surface.height)) throw std::runtime_error("checkpoint: RNG state layout differs");
+        const size_t row = (size_t)surface.width * 16, rows = (size_t)surface.height;
+        std::vector<unsigned char> host(std::max(row * rows, (size_t)h.rng_state_count * sizeof(RtRngState)));
+        for (void* s : { surface.surface, surface.last_frame_surface })
+        {
+            if (std::fread(host.data(), row, rows, in.f) != rows) throw std::runtime_error("checkpoint: truncated file");
+            if (cudaMemcpy2D(s, surface.pitch, host.data(), row, row, rows, cudaMemcpyHostToDevice) != cudaSuccess) throw std::runtime_error("checkpoint: surface write failed");
+        }
+        if (std::fread(host.data(), sizeof(RtRngState), h.rng_state_count, in.f) != h.rng_state_count) throw std::runtime_error("checkpoint: truncated file");
+        if (!rng_state && cudaMalloc(&rng_state, (size_t)h.rng_state_count * sizeof(RtRngState)) != cudaSuccess) throw std::runtime_error("allocation failed");
+        if (cudaMemcpy(rng_state, host.data(), (size_t)h.rng_state_count * sizeof(RtRngState), cudaMemcpyHostToDevice) != cudaSuccess) throw std::runtime_error("checkpoint: RNG state write failed");
+        options.samples_per_launch = (int)h.samples_per_launch; options.max_bounces = (int)h.max_bounces;
+        // bring the scene to its clean uploaded state first, so the Samples flag of a freshly built scene does not restart the run
+        scene->GetCamera().SetViewportSize(vec2((float)surface.width, (float)surface.height));
+        scene->Update(0.0f);
+        scene->Upload(rng_state);
+        frame_index = (int)h.frame_index;
     }
 
     unsigned long long CUDARayTracer::GetRayCount() const

@@ -42,6 +42,11 @@ namespace RayTracing
         // memory (host_pitch bytes per row). Replaces the D3D11 present of main.cpp:683-716. Synchronous.
         // Returns the host->device bytes this call moved (GPUScene by value per launch + refreshed spheres/materials).
         size_t RenderToHost(int frames, void* host_pixels, size_t host_pitch);
+        // Progressive-state checkpoint: {frame index, both float4 surfaces, every pixel's XORWOW state}. After
+        // LoadCheckpoint() the next Process() continues the accumulation bit for bit as if the run had never stopped
+        // (the scene itself is not stored: the caller rebuilds it the way it built it before). Both calls synchronise.
+        void SaveCheckpoint(const std::string& path);
+        void LoadCheckpoint(const std::string& path);
         int GetFrameIndex() const { return frame_index; }
         Options& GetOptions() { return options; }
         unsigned long long GetRayCount() const;  // closest-hit queries since construction (device counter, synchronises)

@@ -226,6 +226,19 @@ int rt_host_tracer_render_to_host(RtHostTracer* t, int frames, void* host_pixels
     return Guard([&] { const size_t n = t->tracer->RenderToHost(frames, host_pixels, host_pitch); if (h2d_bytes) *h2d_bytes = n; return RT_OK; });
 }
 
+int rt_host_tracer_save_checkpoint(RtHostTracer* t, const char* path)
+{
+    if (!t || !path) return rt_internal::Fail(RT_E_INVALID, "rt_host_tracer_save_checkpoint: bad argument");
+    return Guard([&] { t->tracer->SaveCheckpoint(path); return RT_OK; });
+}
+
+int rt_host_tracer_load_checkpoint(RtHostTracer* t, const char* path)
+{
+    if (!t || !path) return rt_internal::Fail(RT_E_INVALID, "rt_host_tracer_load_checkpoint: bad argument");
+    if (rt_device_count() <= 0) return rt_internal::Fail(RT_E_CUDA, "rt_host_tracer_load_checkpoint: no CUDA device (there is no CPU fallback)");
+    return Guard([&] { t->tracer->LoadCheckpoint(path); return RT_OK; });
+}
+
 RtHostScene* rt_host_tracer_scene(RtHostTracer* t) { return t ? &t->scene_handle : nullptr; }
 int rt_host_tracer_frame_index(const RtHostTracer* t) { return t ? t->tracer->GetFrameIndex() : -1; }
 

@@ -69,6 +69,11 @@ int rt_host_tracer_on_resize(RtHostTracer* tracer, void* surface, void* last_fra
 /* Headless end-to-end call: restart accumulation, `frames` Process() frames, then the float4 surface -> HOST memory
  * (replaces the D3D11 present, main.cpp:683-716). Synchronous. *h2d_bytes (optional) = host->device bytes moved. */
 int rt_host_tracer_render_to_host(RtHostTracer* tracer, int frames, void* host_pixels, uint64_t host_pitch, uint64_t* h2d_bytes);
+/* Progressive-state checkpoint (the reference keeps this state in RayTracing.cpp:213-234 and main.cpp:634-646 and
+ * loses it on exit): {frame index, both float4 surfaces, all XORWOW states}. A tracer of the same size over the same scene that
+ * loads it continues the accumulation bit for bit. */
+int rt_host_tracer_save_checkpoint(RtHostTracer* tracer, const char* path);
+int rt_host_tracer_load_checkpoint(RtHostTracer* tracer, const char* path);
 RtHostScene* rt_host_tracer_scene(RtHostTracer* tracer);          /* borrowed */
 int rt_host_tracer_frame_index(const RtHostTracer* tracer);
 int rt_host_tracer_set_sampling(RtHostTracer* tracer, int samples_per_launch, int max_bounces, int kernel_variant);

@@ -256,6 +256,47 @@ def test_tracer_facade_process_and_resize(rt, torch_cuda):
     assert tr.frame_index == 1 and (s2[..., 3] == 1).all() and float(s2[..., :3].mean()) > 0
 
 
+def test_checkpoint_resume_continues_bit_for_bit(rt, torch_cuda, tmp_path):
+    """{frame index, surfaces, RNG states} saved after 3 frames; a NEW tracer that loads the file and renders 2
+    more frames ends on exactly the image (and RNG stream position) of the uninterrupted 5-frame run."""
+    t = torch_cuda
+    a = util.assets()
+    W, H = 80, 56
+
+    def make():
+        s = t.zeros((H, W, 4), dtype=t.float32, device="cuda"); l = t.zeros_like(s)
+        tr = rt.Tracer(s, l, W, H, W * 16, bunny_obj=a["obj"], env_dds=a["dds"], seed=77, samples_per_launch=3, max_bounces=4)
+        tr.scene.set_camera(*util.POSES["poseB"], W, H)
+        return tr, s, l
+
+    tr, s, l = make()
+    for _ in range(3):
+        tr.process()
+    path = str(tmp_path / "run.ckpt")
+    tr.save_checkpoint(path)
+    for _ in range(2):
+        tr.process()
+    t.cuda.synchronize()
+    full = s.clone()
+    assert tr.frame_index == 5
+
+    tr2, s2, l2 = make()
+    tr2.load_checkpoint(path)
+    assert tr2.frame_index == 3
+    for _ in range(2):
+        tr2.process()
+    t.cuda.synchronize()
+    assert tr2.frame_index == 5
+    assert t.equal(s2, full) and t.equal(l2, full)
+    # a third run without the checkpoint differs after 2 frames (the test would otherwise pass vacuously)
+    tr3, s3, _ = make()
+    tr3.process(); tr3.process()
+    t.cuda.synchronize()
+    assert not t.equal(s3, full)
+    with pytest.raises(RuntimeError):
+        tr3.load_checkpoint(str(tmp_path / "missing.ckpt"))
+
+
 def test_ambient_occlusion_and_tonemap(rt, torch_cuda):
     t = torch_cuda
     d = gpu_util.DeviceScene(rt, t, 160, 120, "poseB", seed=3, env=False)

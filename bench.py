@@ -106,7 +106,7 @@ class CpuReference:
 
     def sample_desc(self, stride, spp):
         a = self.a
-        return (f"every {stride}th row of the {a.width}x{a.height} frame ({(a.height + stride - 1) // stride} rows), {spp} spp, "
+        return (f"every {stride}{ {1: 'st', 2: 'nd', 3: 'rd'}.get(stride, 'th')} row of the {a.width}x{a.height} frame ({(a.height + stride - 1) // stride} rows), {spp} spp, "
                 f"{a.bounces} bounces, reference raytracing_kernel_main body host-compiled (-O3, OpenMP)")
 
 

@@ -2,6 +2,9 @@
 #include <cstdio>
 #include <cstring>
 #include <map>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -84,6 +87,8 @@ int rt_accel_create(const RtBVHNode* nodes, uint32_t node_count, const uint32_t*
     AccelHost host;
     if (int r = BuildAccelHost(nodes, node_count, face_indices, faces, face_count, vertices, vertex_count, fat_leaf_threshold, host))
         return Fail(r, r == RT_E_DEPTH ? "rt_accel_create: BVH deeper than the traversal stack" : "rt_accel_create: inconsistent BVH/scene arrays");
+    const bool timing = getenv("B200RT_BVH_TIMING") != nullptr;
+    const auto t_upload = std::chrono::steady_clock::now();
     RtAccel* a = new RtAccel();
     WideNode* d_wide = nullptr; TriRecord* d_tris = nullptr; ShadeRecord* d_shade = nullptr; RtBVHNode* d_ref = nullptr;
     const size_t bw = host.wide.size() * sizeof(WideNode), bt = host.tris.size() * sizeof(TriRecord);
@@ -101,6 +106,7 @@ int rt_accel_create(const RtBVHNode* nodes, uint32_t node_count, const uint32_t*
         cudaFree(d_wide); cudaFree(d_tris); cudaFree(d_shade); cudaFree(d_ref); delete a;
         return CudaFail(e, "rt_accel_create upload");
     }
+    if (timing) fprintf(stderr, "[accel] %-20s %8.1f ms (%.0f MB)\n", "upload", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_upload).count(), (bw + bt + bs + br) / 1e6);
     a->view.wide = d_wide; a->view.tris = d_tris; a->view.shade = d_shade; a->view.ref_nodes = d_ref;
     a->view.root_ref = host.root_ref; a->view.node_count = node_count;
     a->device_bytes = bw + bt + bs + br;

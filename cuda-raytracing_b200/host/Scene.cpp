@@ -93,7 +93,9 @@ namespace RayTracing
 
     void Scene::BuildBVH()
     {
+        if (bvh_current && bvh) return;  // nothing changed since the last build (an explicit BuildBVH() followed by Upload())
         if (!bvh) bvh = std::make_unique<BVH>();
         bvh->Calculate(vertices, faces);
+        bvh_current = true;
     }
 }

@@ -84,7 +84,7 @@ namespace RayTracing
         size_t RefreshDynamic();
 
         Camera& GetCamera() { return camera; }
-        void AddDirtyFlags(DirtyFlags flags = ~0u) { dirty_flags |= flags; }
+        void AddDirtyFlags(DirtyFlags flags = ~0u) { dirty_flags |= flags; if (flags & static_cast<DirtyFlags>(DirtyFlagValue::BVH)) bvh_current = false; }
         void AddDirtyFlag(DirtyFlagValue flag) { AddDirtyFlags(static_cast<DirtyFlags>(flag)); }
         DirtyFlags GetDirtyFlags() const { return dirty_flags; }
         bool IsFlagDirty(DirtyFlagValue flag) const { return dirty_flags & static_cast<DirtyFlags>(flag); }
@@ -106,6 +106,7 @@ namespace RayTracing
         std::vector<RtVertex> vertices;
         std::unique_ptr<BVH> bvh;
         DirtyFlags dirty_flags = ~0u;
+        bool bvh_current = false;  // BuildBVH() ran after the last geometry change (Upload() then does not build again)
         std::string env_path;
         // device side (owned; released in ~Scene through the C ABI)
         void* d_spheres = nullptr; void* d_materials = nullptr; void* d_nodes = nullptr;

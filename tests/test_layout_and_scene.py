@@ -90,6 +90,34 @@ def test_small_scenes_bvh_vs_reference(rt, ref):
         assert np.array_equal(util.raw(a["nodes"]), nodes) and np.array_equal(a["face_indices"], fi)
 
 
+def test_parallel_bvh_build_adversarial_soup_vs_reference(rt, ref):
+    """The parallel builder (level-synchronous top tree + per-thread subtrees + block renumbering, host/BVH.cpp) against the
+    reference's recursive BVH.cpp on a soup that exercises every branch: several top-tree levels (120 k triangles > 7 subtrees),
+    an unsplittable leaf LARGER than a subtree (20 k identical triangles stay one top-tree leaf), clusters of different density,
+    triangles much larger than their neighbours, and axis fallbacks (flat clusters)."""
+    rng = np.random.default_rng(11)
+    scene = rt.Scene()
+    m = scene.add_material()
+    tris = []
+    for centre, spread, n in (((0, 0, 0), 20.0, 60000), ((50, 5, -30), 2.0, 30000), ((-40, -10, 10), 0.5, 10000)):
+        c = rng.normal(size=(n, 1, 3)) * spread + np.asarray(centre)
+        tris.append(c + rng.normal(size=(n, 3, 3)) * 0.3)
+    flat = rng.uniform(-30, 30, size=(2000, 1, 3)); flat[..., 1] = 7.0           # coplanar sheet: y extent 0 for its nodes
+    tris.append(flat + rng.normal(size=(2000, 3, 3)) * np.asarray([0.5, 0.0, 0.5]))
+    tris.append(np.repeat(np.asarray([[[3.0, 3.0, 3.0], [4.0, 3.0, 3.0], [3.0, 4.0, 3.0]]]), 20000, axis=0))  # 20 k identical
+    tris.append(np.asarray([[[-200.0, -50.0, -200.0], [200.0, -50.0, -200.0], [0.0, -50.0, 300.0]]]))         # one giant triangle
+    soup = np.concatenate(tris).astype(np.float32)
+    soup = soup[rng.permutation(len(soup))]
+    for t in soup:
+        scene.add_triangle(t[0], t[1], t[2], m)
+    scene.build_bvh()
+    a = scene.arrays()
+    nodes, fi = ref.bvh_build(util.raw(a["vertices"]), util.raw(a["faces"]))
+    assert np.array_equal(a["face_indices"], fi)
+    assert np.array_equal(util.raw(a["nodes"]), nodes)
+    assert a["nodes"]["prim_count"].max() >= 20000
+
+
 def test_golden_hashes(rt, bunny):
     """Runs everywhere (no /root/reference needed): arrays hash to what the GLM + BVH.cpp build produced."""
     h = json.load(open(os.path.join(util.GOLDEN, "scene_hashes.json")))

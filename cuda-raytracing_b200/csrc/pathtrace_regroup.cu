@@ -30,12 +30,13 @@ namespace
         int frame_index, spp, max_bounces, blend_mode, write_last;
         unsigned long long* ray_counter;
         unsigned int* pixel_counter;  // zeroed before the launch
-        int refill;                   // regroup threshold (lanes)
+        int refill, leaf_batch;       // regroup thresholds (lanes): shade/refill, triangle step
         PathConsts consts;
     };
 
     enum : int { ST_NEED = 0, ST_TRAV = 1, ST_DONE = 2 };
     constexpr int kRefill = 12;     // shade/refill as soon as this many lanes are parked
+    constexpr int kLeafBatch = 8;   // run the triangle step as soon as this many lanes sit on a leaf
 
     __device__ __forceinline__ void camera_ray_rg(const RtCamera& cam, float u, float v, Vec3& o, Vec3& d)
     {
@@ -85,12 +86,13 @@ __global__ void __launch_bounds__(256, kMinBlocks) pathtrace_regroup_kernel(Acce
     HitRecord h; h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
     Vec3 nd = mk3(0, 0, 1);
     // conservative slab test in FMA form: t = fma(plane, inv, c), c = -(o * inv); abs error <= slack (see DESIGN.md "box culls")
-    float ix = 0, iy = 0, iz = 0, cx = 0, cy = 0, cz = 0, k2 = 0, start_length = 1e30f;
+    float2 i_xy = make_float2(0, 0), i_zz = i_xy, no_xy = i_xy, no_zz = i_xy;  // per-ray constant pairs of the packed slab test
+    float start_length = 1e30f;
     uint32_t node = RT_SENTINEL;     // current node reference (inner, leaf with its remaining range, or sentinel)
     int sp = 0;
     uint32_t stack[RT_STACK_SIZE];
     unsigned rays = 0;
-    const float kFoldK1 = 1.0f + 2.5e-6f, big = 1e30f;
+    const float kWiden = 1.0e-6f, big = 1e30f;
 
     for (;;)
     {
@@ -158,57 +160,65 @@ __global__ void __launch_bounds__(256, kMinBlocks) pathtrace_regroup_kernel(Acce
                 h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
                 sphere_tests(S.spheres, S.sphere_count, ps.o, nd, h);
                 start_length = h.t;
-                ix = nd.x != 0.0f ? 1.0f / nd.x : big; iy = nd.y != 0.0f ? 1.0f / nd.y : big; iz = nd.z != 0.0f ? 1.0f / nd.z : big;
-                const float ax = ps.o.x * ix, ay = ps.o.y * iy, az = ps.o.z * iz;
-                cx = -ax; cy = -ay; cz = -az;
-                k2 = 2.1f * (4.0e-7f * fmaxf(fabsf(ax), fmaxf(fabsf(ay), fabsf(az))) + 1e-30f);
+                const float ix = nd.x != 0.0f ? 1.0f / nd.x : big, iy = nd.y != 0.0f ? 1.0f / nd.y : big, iz = nd.z != 0.0f ? 1.0f / nd.z : big;
+                i_xy = make_float2(ix, iy); i_zz = make_float2(iz, iz);
+                no_xy = make_float2(-ps.o.x, -ps.o.y); no_zz = make_float2(-ps.o.z, -ps.o.z);
                 sp = 0; stack[sp++] = RT_SENTINEL;
                 node = A.root_ref;
                 state = ST_TRAV; rays++;
             }
         }
 
-        // ---------------- traversal: ONE step per lane and iteration, if-if (a wide node, or one triangle of a leaf) ----------------
-        // No inner loop to wait in and nothing speculative: the per-ray work is the megakernel's, node for node.
-        if (state == ST_TRAV)
+        // ---------------- traversal: ONE step per lane and iteration (a wide node, or one triangle of a leaf) ----------------
+        // Nothing speculative: the per-ray work is the megakernel's, node for node. Node steps run every iteration; the triangle
+        // step is voted: lanes that sit on a leaf wait until leaf_batch of them do (or nobody has a node step left). Waiting is
+        // free here - unlike in the megakernel, no other lane's critical path depends on it, the parked capacity is refilled.
+        const bool trav = state == ST_TRAV;
+        const bool on_leaf = trav && (node & RT_LEAF_BIT);
+        const unsigned m_leaf = __ballot_sync(FULL, on_leaf), m_inner = __ballot_sync(FULL, trav && !on_leaf);
+        if (trav && !on_leaf)
         {
-            if (!(node & RT_LEAF_BIT))
+            const WideNode* w = A.wide + node;
+            const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32);
+            const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
+            // exact slab form (plane - o) * inv in packed fp32, three-compare conservative cull (traverse.cuh)
+            const float2 d0 = __fmul2_rn(__fadd2_rn(make_float2(a.x, a.y), no_xy), i_xy), d1 = __fmul2_rn(__fadd2_rn(make_float2(a.z, a.w), no_xy), i_xy);
+            const float2 d2 = __fmul2_rn(__fadd2_rn(make_float2(b.x, b.y), no_xy), i_xy), d3 = __fmul2_rn(__fadd2_rn(make_float2(b.z, b.w), no_xy), i_xy);
+            const float2 d4 = __fmul2_rn(__fadd2_rn(make_float2(c.x, c.y), no_zz), i_zz), d5 = __fmul2_rn(__fadd2_rn(make_float2(c.z, c.w), no_zz), i_zz);
+            const float mn0 = fmaxf(fmaxf(fminf(d0.x, d1.x), fminf(d0.y, d1.y)), fminf(d4.x, d4.y));
+            const float mx0 = fminf(fminf(fmaxf(d0.x, d1.x), fmaxf(d0.y, d1.y)), fmaxf(d4.x, d4.y));
+            const float mn1 = fmaxf(fmaxf(fminf(d2.x, d3.x), fminf(d2.y, d3.y)), fminf(d5.x, d5.y));
+            const float mx1 = fminf(fminf(fmaxf(d2.x, d3.x), fmaxf(d2.y, d3.y)), fmaxf(d5.x, d5.y));
+            const float lo0 = fmaf(-kWiden, fabsf(mn0), mn0), hi0 = fmaf(kWiden, fabsf(mx0), mx0);
+            const float lo1 = fmaf(-kWiden, fabsf(mn1), mn1), hi1 = fmaf(kWiden, fabsf(mx1), mx1);
+            const bool hit0 = hi0 >= lo0 && lo0 <= h.t && hi0 > 0.0f;
+            const bool hit1 = hi1 >= lo1 && lo1 <= h.t && hi1 > 0.0f;
+            if (hit0 && hit1)
             {
-                const WideNode* w = A.wide + node;
-                const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32);
-                const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
-                float t1 = fmaf(a.x, ix, cx), t2 = fmaf(a.z, ix, cx);
-                float mn0 = fminf(t1, t2), mx0 = fmaxf(t1, t2);
-                t1 = fmaf(a.y, iy, cy); t2 = fmaf(a.w, iy, cy);
-                float mnb = fminf(t1, t2), mxb = fmaxf(t1, t2);
-                t1 = fmaf(c.x, iz, cz); t2 = fmaf(c.y, iz, cz);
-                mn0 = fmaxf(fmaxf(mn0, mnb), fminf(t1, t2)); mx0 = fminf(fminf(mx0, mxb), fmaxf(t1, t2));
-                t1 = fmaf(b.x, ix, cx); t2 = fmaf(b.z, ix, cx);
-                float mn1 = fminf(t1, t2), mx1 = fmaxf(t1, t2);
-                t1 = fmaf(b.y, iy, cy); t2 = fmaf(b.w, iy, cy);
-                mnb = fminf(t1, t2); mxb = fmaxf(t1, t2);
-                t1 = fmaf(c.z, iz, cz); t2 = fmaf(c.w, iz, cz);
-                mn1 = fmaxf(fmaxf(mn1, mnb), fminf(t1, t2)); mx1 = fminf(fminf(mx1, mxb), fmaxf(t1, t2));
-                // folded conservative cull (traverse.cuh, RT_TW_FOLD): max(entry, 0) <= widen(min(exit, best))
-                const bool hit0 = fmaxf(mn0, 0.0f) <= fmaf(fminf(mx0, h.t), kFoldK1, k2);
-                const bool hit1 = fmaxf(mn1, 0.0f) <= fmaf(fminf(mx1, h.t), kFoldK1, k2);
-                if (hit0 && hit1)
-                {
-                    const bool swap = mn1 < mn0;
-                    stack[sp++] = swap ? ch.x : ch.y;
-                    node = swap ? ch.y : ch.x;
-                }
-                else if (hit0) node = ch.x;
-                else if (hit1) node = ch.y;
-                else node = stack[--sp];
+                const bool swap = mn1 < mn0;
+                stack[sp++] = swap ? ch.x : ch.y;
+                node = swap ? ch.y : ch.x;
             }
-            else
-            {   // one triangle; the leaf reference is re-encoded with the remaining range
-                leaf_tests<true, false>(A, node & 0x07FFFFFFu, 1u, ps.o, ps.d, nd, start_length, h);
-                if (node & 0x78000000u) node = node - (1u << 27) + 1u;
-                else node = stack[--sp];
+            else if (hit0) node = ch.x;
+            else if (hit1) node = ch.y;
+            else node = stack[--sp];
+        }
+        if (on_leaf && (__popc(m_leaf) >= P.leaf_batch || m_inner == 0u))
+        {   // one triangle; the leaf reference is re-encoded with the remaining range. No per-candidate leaf-box check (deferred).
+            leaf_tests<false, false>(A, node & 0x07FFFFFFu, 1u, ps.o, ps.d, nd, start_length, h);
+            if (node & 0x78000000u) node = node - (1u << 27) + 1u;
+            else node = stack[--sp];
+        }
+        if (trav && node == RT_SENTINEL)
+        {   // ray finished: the reference only counts a triangle whose leaf box passes (main_raytracing.cu:46) - checked once, on the
+            // winner; if it fails (grazing within rounding, rare) the ray is redone with the per-candidate check
+            if (h.id != RT_MISS_ID && !(h.id & RT_SPHERE_ID_BIT) && !exact_box(ps.o, ps.d, A.ref_nodes + __ldg(&A.tris[h.slot].ref_leaf), start_length))
+            {
+                h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
+                sphere_tests(S.spheres, S.sphere_count, ps.o, nd, h);
+                trace_wide_checked<false, false>(A, ps.o, ps.d, nd, h);
             }
-            if (node == RT_SENTINEL) { state = ST_NEED; have_hit = true; }
+            state = ST_NEED; have_hit = true;
         }
     }
 
@@ -228,8 +238,9 @@ cudaError_t LaunchPathTraceRegroup(const AccelView& accel, const SceneView& scen
     P.width = p.width; P.height = p.height; P.pitch = p.pitch; P.frame_index = p.frame_index;
     P.spp = p.samples_per_launch; P.max_bounces = p.max_bounces; P.blend_mode = p.blend_mode; P.write_last = p.write_last_frame;
     P.ray_counter = p.d_ray_counter; P.pixel_counter = d_pixel_counter;
-    P.refill = kRefill;
+    P.refill = kRefill; P.leaf_batch = kLeafBatch;
     if (const char* v = getenv("B200RT_REFILL")) P.refill = atoi(v);        // tuning hooks (profiles/ sweeps)
+    if (const char* v = getenv("B200RT_LEAF_BATCH")) P.leaf_batch = atoi(v);
     {   // glm quat(vec3(0, PI, 0)), type_quat.inl:204-213, in host fp32 like the oracle
         const float PI = 3.1415926536f;
         const float cx = std::cos(0.0f * 0.5f), cy = std::cos(PI * 0.5f), cz = std::cos(0.0f * 0.5f);

@@ -154,6 +154,9 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
 #ifndef RT_TW_FOLD
 #define RT_TW_FOLD 1
 #endif
+#ifndef RT_TW_PREFETCH_CHILD
+#define RT_TW_PREFETCH_CHILD 0
+#endif
 #ifndef RT_TW_PACKED
 #define RT_TW_PACKED 1
 #endif
@@ -237,6 +240,13 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
     } while (0)
 #define RT_NODE_MATH(a, b, c, ch)                                                                                          \
     do {                                                                                                                    \
+        if (RT_TW_PREFETCH_CHILD)                                                                                           \
+        {   /* experiment: start the L2->L1 fetch of both children's records while this node's boxes are tested */        \
+            const char* c0 = (ch.x & RT_LEAF_BIT) ? reinterpret_cast<const char*>(A.tris + (ch.x & 0x07FFFFFFu)) : reinterpret_cast<const char*>(A.wide + ch.x); \
+            const char* c1 = (ch.y & RT_LEAF_BIT) ? reinterpret_cast<const char*>(A.tris + (ch.y & 0x07FFFFFFu)) : reinterpret_cast<const char*>(A.wide + ch.y); \
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(c0));                                                             \
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(c1));                                                             \
+        }                                                                                                                   \
         if (kFma && RT_TW_AXIS_SLACK)                                                                                       \
         {                                                                                                                   \
             const float en0 = fmaxf(fmaxf(fmaf(neg_x ? a.z : a.x, ix, cnx), fmaf(neg_y ? a.w : a.y, iy, cny)), fmaf(neg_z ? c.y : c.x, iz, cnz)); \

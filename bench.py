@@ -299,9 +299,18 @@ def run_b200_arm(a):
 
     peak, peak_src = measured_peaks()
     traffic = None  # dram bytes per launch from the committed ncu capture of this exact launch shape (never measured under bench)
+    issue = None    # what actually bounds the kernel: warp instructions per launch (same capture) against the SMs' issue rate
     try:
         if a.variant == 0 and (a.width, a.height, a.spp_per_launch, a.bounces, a.pose) == (1920, 1080, 64, 4, "poseB"):
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["pathtrace_megakernel"]["dram_bytes_per_launch"]
+            cap = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["pathtrace_megakernel"]
+            traffic = cap["dram_bytes_per_launch"]
+            props = torch.cuda.get_device_properties(dev)
+            mhz = (clocks or {}).get("sm_mhz") or 1965.0
+            peak_ginst = props.multi_processor_count * 4 * mhz * 1e-3  # 4 schedulers per SM, 1 warp instruction per clock each
+            ach_ginst = cap["warp_instructions_per_launch"] / ((kern_ms / launches_per_step / a.steps) * 1e-3) / 1e9
+            issue = {"achieved": ach_ginst, "peak": peak_ginst, "unit": "G warp-inst/s", "frac": ach_ginst / peak_ginst,
+                     "threads_per_instruction": cap["threads_per_instruction"],
+                     "source": "instruction count from the committed ncu capture (profiles/traffic.json), time and SM clock live"}
     except Exception:
         traffic = None
     launches = a.steps * launches_per_step
@@ -318,7 +327,7 @@ def run_b200_arm(a):
                    "rays_per_step": rays_all / a.steps, "ms_per_frame_64spp": step_ms / a.steps, "wall_s": wall},
         "clocks": clocks, "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                     "kernel": "pathtrace_megakernel", "peak_source": peak_src,
+                     "kernel": "pathtrace_megakernel", "peak_source": peak_src, "issue": issue,
                      "bytes_per_ray": bytes_per_ray, "nodes_per_ray_reference_order": nodes_per_ray, "tris_per_ray_reference_order": tris_per_ray,
                      "note": "algorithmic bytes = rays x (32 B x nodes + 48 B x tris under the REFERENCE traversal order + 64) + pixels x 80; "
                              "the bunny scene is L2-resident, so frac > 1 means cache/culling amplification, not HBM traffic (SURVEY §8d)"},

@@ -12,6 +12,9 @@
 #include <cstdlib>
 #include "shade.cuh"
 
+#ifndef RT_PT_BLOCK
+#define RT_PT_BLOCK 128  // threads per CTA of the megakernel: 256 / 128 / 64 = 57.0 / 56.0 / 56.8 ms (finer-grained tail of the last wave)
+#endif
 #ifndef RT_PT_FMA
 #define RT_PT_FMA 0  // 1: slab test of the path tracer in FMA form (traverse.cuh, kFma): 1 % faster on the bunny, 1.9x slower on config 4b
 #endif
@@ -61,11 +64,11 @@ __device__ __forceinline__ void write_pixel(const FrameParams& P, int x, int y, 
 // kMode 0: product traversal. kMode 2: reference-order traversal with work counters (measurement of the
 // algorithmic bytes per ray; same image up to exact-tie resolution).
 template <int kMode, int kMinBlocks, bool kLockstep = false>
-__global__ void __launch_bounds__(256, kMinBlocks) pathtrace_megakernel(AccelView A, SceneView S, FrameParams P)
+__global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK)) pathtrace_megakernel(AccelView A, SceneView S, FrameParams P)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int x = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
-    const int y = blockIdx.y * 16 + (warp >> 1) * 4 + (lane >> 3);
+    const int y = blockIdx.y * (RT_PT_BLOCK / 16) + (warp >> 1) * 4 + (lane >> 3);  // CTA = 16 x (RT_PT_BLOCK / 16) pixels, warp = 8 x 4
     const bool active = x < P.width && y < P.height;
     unsigned rays = 0;
     uint32_t work_nodes = 0, work_tris = 0;
@@ -140,7 +143,8 @@ cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, cons
         P.consts.qy = cx * sy * cz + sx * cy * sz;
         P.consts.qz = cx * cy * sz - sx * sy * cz;
     }
-    const dim3 grid((p.width + 15) / 16, (p.height + 15) / 16), block(256);
+    const int tile_h = RT_PT_BLOCK / 16;
+    const dim3 grid((p.width + 15) / 16, (p.height + tile_h - 1) / tile_h), block(RT_PT_BLOCK);
     static int min_blocks = 0;
     if (!min_blocks) { const char* v = getenv("B200RT_MINBLOCKS"); min_blocks = v ? atoi(v) : 5; }  // occupancy sweep hook (profiles/)
     if (p.variant == 2) pathtrace_megakernel<2, 3><<<grid, block, 0, stream>>>(accel, scene, P);

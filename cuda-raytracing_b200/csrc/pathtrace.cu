@@ -221,3 +221,13 @@ cudaError_t LaunchAmbientOcclusion(const AccelView& accel, const SceneView& scen
     ambient_occlusion_kernel<<<grid, block, 0, stream>>>(accel, scene, width, height, ao_rays, d_ao, d_ray_counter);
     return cudaGetLastError();
 }
+
+#if defined(RT_TW_MODE) && RT_TW_MODE == 8
+// measurement build only: read (and optionally clear) the lane histogram of this TU's kernels
+extern "C" int rt_debug_tw_hist(unsigned long long* out66, int reset)
+{
+    if (cudaMemcpyFromSymbol(out66, g_tw_hist, sizeof(unsigned long long) * 66) != cudaSuccess) return -1;
+    if (reset) { unsigned long long zero[66] = {}; if (cudaMemcpyToSymbol(g_tw_hist, zero, sizeof(zero)) != cudaSuccess) return -1; }
+    return 0;
+}
+#endif

@@ -102,6 +102,10 @@ __device__ __forceinline__ bool accept(float t, uint32_t key, const HitRecord& h
 }
 
 // One triangle record (already loaded) against the ray: glm test, tie rule, optional per-candidate exact leaf-box check.
+#if defined(RT_TW_MODE) && RT_TW_MODE == 8
+static __device__ unsigned long long g_tw_hist[66];  // [n] iterations with n lanes alive; [33 + n] pending stack entries summed
+#endif
+
 template <bool kLazyExactBox, bool kTieById>
 __device__ __forceinline__ void leaf_test_one(const AccelView& A, float4 r0, float4 r1, float4 r2, uint32_t slot, Vec3 o, Vec3 d, Vec3 nd,
                                               float start_length, HitRecord& h, uint32_t* verified_leaf = nullptr)
@@ -389,6 +393,39 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
             leaf_test_one<!kDeferred, kTieById>(A, q0, q1, q2, slot, o, d, nd, start_length, h, verified_ptr);
             if (node & 0x78000000u) node = node - (1u << 27) + 1u;
             else RT_POP();
+        }
+    }
+#elif RT_TW_MODE == 8
+    // measurement build (benchmarks/lane_histogram.py): mode 7 stepped warp-synchronously, with a histogram of how many lanes
+    // still have a ray per iteration and of their pending stack entries. Not a product mode.
+    {
+        const unsigned entry = __activemask();
+        for (;;)
+        {
+            const bool busy = node != RT_SENTINEL;
+            const unsigned alive = __ballot_sync(entry, busy);
+            if (alive == 0u) break;
+            const unsigned pending = __reduce_add_sync(entry, busy ? (unsigned)(sp - 1) : 0u);
+            if ((threadIdx.x & 31) == (__ffs(entry) - 1))
+            {
+                atomicAdd(&g_tw_hist[__popc(alive)], 1ull);
+                atomicAdd(&g_tw_hist[33 + __popc(alive)], (unsigned long long)pending);
+            }
+            if (busy)
+            {
+                const bool is_leaf = (node & RT_LEAF_BIT) != 0u;
+                const uint32_t slot = node & 0x07FFFFFFu;
+                const char* rec = is_leaf ? reinterpret_cast<const char*>(A.tris + slot) : reinterpret_cast<const char*>(A.wide + node);
+                const float4 q0 = ldg4(rec), q1 = ldg4(rec + 16), q2 = ldg4(rec + 32);
+                const uint2 q3 = __ldg(reinterpret_cast<const uint2*>(rec + 48));
+                if (!is_leaf) RT_NODE_MATH(q0, q1, q2, q3);
+                else
+                {
+                    leaf_test_one<!kDeferred, kTieById>(A, q0, q1, q2, slot, o, d, nd, start_length, h, verified_ptr);
+                    if (node & 0x78000000u) node = node - (1u << 27) + 1u;
+                    else RT_POP();
+                }
+            }
         }
     }
 #elif RT_TW_MODE == 6

@@ -128,6 +128,23 @@ __device__ __forceinline__ void leaf_test_one(const AccelView& A, float4 r0, flo
     h.t = t; h.id = id; h.slot = slot; h.key = key; h.bu = bu; h.bv = bv;
 }
 
+// Same, for the deferred-check traversal with the hit details (id, slot, key, u, v) parked in shared memory: only the best t stays
+// in a register across the traversal loop (the kernel runs at a 48-register cap; the details are written ~once per ray).
+// sh points at this thread's column of a [5][blockDim] array; stride = blockDim.x.
+template <bool kTieById>
+__device__ __forceinline__ void leaf_test_one_parked(float4 r0, float4 r1, float4 r2, uint32_t slot, Vec3 o, Vec3 nd, float& best_t,
+                                                     uint32_t* sh, uint32_t stride)
+{
+    float t, bu, bv;
+    if (!tri_test(o, nd, r0, r1, r2, t, bu, bv)) return;
+    if (t > best_t || t < 0.0f) return;
+    const uint32_t id = __float_as_uint(r0.w);
+    const uint32_t key = kTieById ? id : __float_as_uint(r2.w);
+    if (!(t < best_t) && !(key < sh[2 * stride] && !(sh[0] & RT_SPHERE_ID_BIT))) return;  // exact tie: accept()'s key rule
+    best_t = t;
+    sh[0] = id; sh[stride] = slot; sh[2 * stride] = key; sh[3 * stride] = __float_as_uint(bu); sh[4 * stride] = __float_as_uint(bv);
+}
+
 template <bool kLazyExactBox, bool kTieById>
 __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, uint32_t count, Vec3 o, Vec3 d, Vec3 nd,
                                            float start_length, HitRecord& h, uint32_t* verified_leaf = nullptr)
@@ -160,6 +177,12 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
 #endif
 #ifndef RT_TW_PREFETCH_CHILD
 #define RT_TW_PREFETCH_CHILD 0
+#endif
+#ifndef RT_TW_PARK
+#define RT_TW_PARK 0
+#endif
+#ifndef RT_TW_CULL
+#define RT_TW_CULL 0   /* only wired into RT_TW_MODE 7 (tcut refresh) */
 #endif
 #ifndef RT_TW_PACKED
 #define RT_TW_PACKED 1
@@ -224,6 +247,8 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
     // k1 = (1 + kWiden) / (1 - kWiden) and k2 = 2 slack / (1 - kWiden), both rounded up, move the whole widening onto the exit side,
     // so the entry side needs none (a superset of the two-sided form term by term; -6 instructions per wide node).
     const float k1 = 1.0f + 2.5e-6f, k2 = 2.1f * slack;
+    const float kExitWiden = 1.0f + 3.0e-6f, kBestWiden = 1.0f + 2.0e-6f;
+    float tcut = h.t * kBestWiden;  // RT_TW_CULL: refreshed whenever a triangle step may have changed h.t
     // RT_TW_AXIS_SLACK (kFma only): the absolute error of fma(plane, inv, -(o*inv)) is ~ulp(|o*inv|) of THAT axis, and |o*inv| is
     // huge exactly on the axes the ray is nearly perpendicular to. One slack = the max over the axes (above) makes every entry/exit
     // that wrong: on the 13.9 M-triangle grid (coordinates ~300, many near-axis-parallel rays) it is larger than the leaves and the
@@ -311,6 +336,12 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
             hit0 = fmaxf(mn0, 0.0f) <= fmaf(fminf(mx0, h.t), k1, k2);                                                       \
             hit1 = fmaxf(mn1, 0.0f) <= fmaf(fminf(mx1, h.t), k1, k2);                                                       \
         }                                                                                                                   \
+        else if (RT_TW_CULL && !kFma)                                                                                      \
+        {   /* exact slab form: only relative errors. exit * (1+3k) >= entry, entry <= best * (1+2k) (= tcut, kept per ray),    \
+               exit > 0: term by term a superset of the two-sided widening below, 4 instead of 7 instructions per child */  \
+            hit0 = mx0 * kExitWiden >= mn0 && mn0 <= tcut && mx0 > 0.0f;                                                    \
+            hit1 = mx1 * kExitWiden >= mn1 && mn1 <= tcut && mx1 > 0.0f;                                                    \
+        }                                                                                                                   \
         else                                                                                                                \
         {   /* widen (superset of the reference's divisions), cull against the current best */                             \
             const float lo0 = fmaf(-kWiden, fabsf(mn0), mn0) - slack, hi0 = fmaf(kWiden, fabsf(mx0), mx0) + slack;          \
@@ -330,6 +361,18 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
     } while (0)
 #define RT_LEAF_STEP(ref) leaf_tests<!kDeferred, kTieById>(A, (ref) & 0x07FFFFFFu, (((ref) >> 27) & 0xFu) + 1u, o, d, nd, start_length, h, verified_ptr)
 
+#if RT_TW_PARK && RT_TW_MODE == 7
+    __shared__ uint32_t park_store[5 * 256];  // blocks of this library's traversal kernels have at most 256 threads
+    uint32_t* const park = park_store + threadIdx.x;
+    const uint32_t park_stride = blockDim.x;
+    if (kDeferred)
+    {
+        park[0] = h.id; park[park_stride] = h.slot; park[2 * park_stride] = h.key;
+        park[3 * park_stride] = __float_as_uint(h.bu); park[4 * park_stride] = __float_as_uint(h.bv);
+    }
+#else
+    uint32_t* const park = nullptr; const uint32_t park_stride = 0;
+#endif
 #if RT_TW_MODE == 1
     // if-if: one node of either kind per iteration, no inner loop to wait in
     while (node != RT_SENTINEL)
@@ -390,10 +433,17 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
         if (!is_leaf) RT_NODE_MATH(q0, q1, q2, q3);
         else
         {
-            leaf_test_one<!kDeferred, kTieById>(A, q0, q1, q2, slot, o, d, nd, start_length, h, verified_ptr);
+            if (RT_TW_PARK && kDeferred) leaf_test_one_parked<kTieById>(q0, q1, q2, slot, o, nd, h.t, park, park_stride);
+            else leaf_test_one<!kDeferred, kTieById>(A, q0, q1, q2, slot, o, d, nd, start_length, h, verified_ptr);
+            tcut = h.t * kBestWiden;
             if (node & 0x78000000u) node = node - (1u << 27) + 1u;
             else RT_POP();
         }
+    }
+    if (RT_TW_PARK && kDeferred)
+    {
+        h.id = park[0]; h.slot = park[park_stride]; h.key = park[2 * park_stride];
+        h.bu = __uint_as_float(park[3 * park_stride]); h.bv = __uint_as_float(park[4 * park_stride]);
     }
 #elif RT_TW_MODE == 8
     // measurement build (benchmarks/lane_histogram.py): mode 7 stepped warp-synchronously, with a histogram of how many lanes

@@ -330,7 +330,7 @@ def run_b200_arm(a):
                      "kernel": "pathtrace_megakernel", "peak_source": peak_src, "issue": issue,
                      "bytes_per_ray": bytes_per_ray, "nodes_per_ray_reference_order": nodes_per_ray, "tris_per_ray_reference_order": tris_per_ray,
                      "note": "algorithmic bytes = rays x (32 B x nodes + 48 B x tris under the REFERENCE traversal order + 64) + pixels x 80; "
-                             "the bunny scene is L2-resident, so frac > 1 means cache/culling amplification, not HBM traffic (SURVEY §8d)"},
+                             "the bunny scene is L2-resident, so frac > 1 means cache/culling amplification, not HBM traffic (SURVEY §8d); `traffic` (ncu, same protocol) includes the write-back of the L2-flush buffer's dirty lines evicted during the launch (~230 MB) on top of surfaces + RNG states + first-touch scene"},
     }
     if e2e:
         line["e2e"] = e2e

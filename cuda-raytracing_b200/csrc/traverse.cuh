@@ -64,30 +64,61 @@ __device__ __forceinline__ bool exact_box(Vec3 o, Vec3 d, const RtBVHNode* node,
 #define RT_SHORT_DIR2 0.99999f
 
 // glm::intersectRayTriangle on a TriRecord. Returns true with (t, bu, bv) when GLM would.
+// kNegO: `o` holds the NEGATED ray origin (the packed slab test keeps -o in registers; using it here as well takes the origin
+// itself out of the traversal loop's live set). Every intermediate is then the exact negation of GLM's (IEEE negation is exact
+// and round-to-nearest is symmetric: fl(-a + b) = -fl(a - b), fl((-a) * b) = -fl(a * b)), the comparisons are mirrored, and the
+// results are negated back: bit-identical t, u, v.
+template <bool kNegO = false>
 __device__ __forceinline__ bool tri_test(Vec3 o, Vec3 nd, float4 r0, float4 r1, float4 r2, float& t, float& bu, float& bv)
 {
     const Vec3 v0 = mk3(r0.x, r0.y, r0.z), e1 = mk3(r1.x, r1.y, r1.z), e2 = mk3(r2.x, r2.y, r2.z);
     const Vec3 p = cross3(nd, e2);
     const float det = dot3(e1, p);
-    const Vec3 dist = o - v0;
-    const float u = dot3(dist, p);
-    const Vec3 perp = cross3(dist, e1);
-    const float v = dot3(nd, perp);
-    if (det > FLT_EPSILON)
+    if (!kNegO)
     {
-        if (u < 0.0f || u > det) return false;
-        if (v < 0.0f || (u + v) > det) return false;
+        const Vec3 dist = o - v0;
+        const float u = dot3(dist, p);
+        const Vec3 perp = cross3(dist, e1);
+        const float v = dot3(nd, perp);
+        if (det > FLT_EPSILON)
+        {
+            if (u < 0.0f || u > det) return false;
+            if (v < 0.0f || (u + v) > det) return false;
+        }
+        else if (det < -FLT_EPSILON)
+        {
+            if (u > 0.0f || u < det) return false;
+            if (v > 0.0f || (u + v) < det) return false;
+        }
+        else return false;
+        const float inv_det = 1.0f / det;
+        t = dot3(e2, perp) * inv_det;
+        bu = u * inv_det; bv = v * inv_det;
+        return true;
     }
-    else if (det < -FLT_EPSILON)
+    else
     {
-        if (u > 0.0f || u < det) return false;
-        if (v > 0.0f || (u + v) < det) return false;
+        const Vec3 ndist = o + v0;                 // = -(origin - v0)
+        const float un = dot3(ndist, p);           // = -u
+        const Vec3 nperp = cross3(ndist, e1);      // = -perp
+        const float vn = dot3(nd, nperp);          // = -v
+        const float ndet = -det;
+        if (det > FLT_EPSILON)
+        {
+            if (un > 0.0f || un < ndet) return false;
+            if (vn > 0.0f || (un + vn) < ndet) return false;
+        }
+        else if (det < -FLT_EPSILON)
+        {
+            if (un < 0.0f || un > ndet) return false;
+            if (vn < 0.0f || (un + vn) > ndet) return false;
+        }
+        else return false;
+        const float inv_det = 1.0f / det;
+        t = -(dot3(e2, nperp) * inv_det);
+        bu = -(un * inv_det); bv = -(vn * inv_det);
+        return true;
     }
-    else return false;
-    const float inv_det = 1.0f / det;
-    t = dot3(e2, perp) * inv_det;
-    bu = u * inv_det; bv = v * inv_det;
-    return true;
 }
 
 // Candidate acceptance: main_raytracing.cu:62 (`distance >= best || distance < 0` rejects). The
@@ -106,12 +137,13 @@ __device__ __forceinline__ bool accept(float t, uint32_t key, const HitRecord& h
 static __device__ unsigned long long g_tw_hist[66];  // [n] iterations with n lanes alive; [33 + n] pending stack entries summed
 #endif
 
-template <bool kLazyExactBox, bool kTieById>
+template <bool kLazyExactBox, bool kTieById, bool kNegO = false>
 __device__ __forceinline__ void leaf_test_one(const AccelView& A, float4 r0, float4 r1, float4 r2, uint32_t slot, Vec3 o, Vec3 d, Vec3 nd,
                                               float start_length, HitRecord& h, uint32_t* verified_leaf = nullptr)
 {
+    static_assert(!(kLazyExactBox && kNegO), "the per-candidate leaf-box check needs the origin itself");
     float t, bu, bv;
-    if (!tri_test(o, nd, r0, r1, r2, t, bu, bv)) return;
+    if (!tri_test<kNegO>(o, nd, r0, r1, r2, t, bu, bv)) return;
     const uint32_t id = __float_as_uint(r0.w);
     const uint32_t key = kTieById ? id : __float_as_uint(r2.w);
     if (!accept(t, key, h)) return;
@@ -177,6 +209,9 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
 #endif
 #ifndef RT_TW_PREFETCH_CHILD
 #define RT_TW_PREFETCH_CHILD 0
+#endif
+#ifndef RT_TW_NEGO
+#define RT_TW_NEGO 0
 #endif
 #ifndef RT_TW_PARK
 #define RT_TW_PARK 0
@@ -434,6 +469,7 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
         else
         {
             if (RT_TW_PARK && kDeferred) leaf_test_one_parked<kTieById>(q0, q1, q2, slot, o, nd, h.t, park, park_stride);
+            else if (RT_TW_NEGO && kDeferred) leaf_test_one<false, kTieById, true>(A, q0, q1, q2, slot, mk3(no_xy.x, no_xy.y, no_zz.x), d, nd, start_length, h, verified_ptr);
             else leaf_test_one<!kDeferred, kTieById>(A, q0, q1, q2, slot, o, d, nd, start_length, h, verified_ptr);
             tcut = h.t * kBestWiden;
             if (node & 0x78000000u) node = node - (1u << 27) + 1u;

@@ -210,6 +210,9 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
 #ifndef RT_TW_PREFETCH_CHILD
 #define RT_TW_PREFETCH_CHILD 0
 #endif
+#ifndef RT_TW_SHSTACK
+#define RT_TW_SHSTACK 0
+#endif
 #ifndef RT_TW_NEGO
 #define RT_TW_NEGO 0
 #endif
@@ -261,14 +264,26 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
 #define RT_SLAB(p, inv, c, oc) (kFma ? fmaf(p, inv, c) : (((p) - (oc)) * (inv)))
     uint32_t stack[RT_STACK_SIZE];
     int sp = 0;
+#if !RT_TW_SHSTACK
     stack[sp++] = RT_SENTINEL;
+#endif
 #if RT_TW_TOS
     uint32_t tos = RT_SENTINEL;
 #define RT_PUSH(x) do { stack[sp++] = tos; tos = (x); } while (0)
 #define RT_POP() (node = tos, tos = stack[--sp])
+#elif RT_TW_SHSTACK
+    // experiment (north-star "shared-memory short stack"): the first RT_TW_SHSTACK entries per thread live in shared memory
+    // ([entry][thread], conflict-free), deeper ones in the local-memory array. Sized for 128-thread CTAs (the megakernel).
+    __shared__ uint32_t sh_stack[RT_TW_SHSTACK * 128];
+    uint32_t* const shs = sh_stack + (threadIdx.x & 127);
+#define RT_PUSH(x) do { if (sp < RT_TW_SHSTACK) shs[sp * 128] = (x); else stack[sp - RT_TW_SHSTACK] = (x); sp++; } while (0)
+#define RT_POP() do { --sp; node = sp < RT_TW_SHSTACK ? shs[sp * 128] : stack[sp - RT_TW_SHSTACK]; } while (0)
 #else
 #define RT_PUSH(x) do { stack[sp++] = (x); } while (0)
 #define RT_POP() (node = stack[--sp])
+#endif
+#if RT_TW_SHSTACK
+    RT_PUSH(RT_SENTINEL);
 #endif
     uint32_t node = A.root_ref;
 #if RT_TW_CACHE

@@ -124,6 +124,17 @@ class Scene:
     def accel_ptr(self):
         return C.c_void_p(lib().rt_host_scene_accel(self.handle))
 
+    def accel_info(self):
+        """rt_accel_info of the re-layout Scene::Upload built (needs upload() first)."""
+        return _accel_info(self.accel_ptr())
+
+
+def _accel_info(handle):
+    v = (C.c_uint64 * 8)()
+    check(lib().rt_accel_info(handle, v))
+    return {"wide_nodes": v[0], "slots": v[1], "ref_leaves": v[2], "fat_leaves": v[3] & 0xFFFFFFFF, "twin_pairs": v[3] >> 32,
+            "wide_depth": v[4], "device_bytes": v[5] | (v[6] << 32), "ref_depth": v[7]}
+
 
 class Accel:
     """RtAccel built directly from host arrays (rt_accel_create)."""
@@ -135,10 +146,7 @@ class Accel:
         self.handle = h
 
     def info(self):
-        v = (C.c_uint64 * 8)()
-        check(lib().rt_accel_info(self.handle, v))
-        return {"wide_nodes": v[0], "slots": v[1], "ref_leaves": v[2], "fat_leaves": v[3], "wide_depth": v[4],
-                "device_bytes": v[5] | (v[6] << 32), "ref_depth": v[7]}
+        return _accel_info(self.handle)
 
     def __del__(self):
         if getattr(self, "handle", None):

@@ -25,6 +25,10 @@
 #define RT_LEAF_BIT 0x80000000u
 #define RT_SENTINEL 0xFFFFFFFFu
 #define RT_MAX_LEAF_PRIMS 16u
+// TriRecord::ref_leaf bit 31: the NEXT slot of the same leaf holds this face's duplicate (same v0, e1/e2 exchanged - the flat copy
+// Scene::AddLoadedScene appends to every smooth face, Scene.cpp:110-127); traverse.cuh skips it after a proven-margin miss.
+#define RT_TWIN_BIT 0x80000000u
+#define RT_REF_LEAF_MASK 0x7FFFFFFFu
 #define RT_STACK_SIZE 64
 
 struct RtFloat4 { float x, y, z, w; };
@@ -43,7 +47,7 @@ struct alignas(64) WideNode
 struct alignas(16) TriRecord
 {
     float v0[3]; uint32_t face_id;
-    float e1[3]; uint32_t ref_leaf;   // index of the reference leaf node (for the exact box re-check)
+    float e1[3]; uint32_t ref_leaf;   // index of the reference leaf node (for the exact box re-check) | RT_TWIN_BIT
     float e2[3]; uint32_t orig_slot; // slot before any fat-leaf permutation (reference visiting order)
 };
 
@@ -61,7 +65,7 @@ struct AccelHost
     std::vector<TriRecord> tris;       // one per BVH slot
     std::vector<ShadeRecord> shade;    // one per BVH slot
     uint32_t root_ref = RT_SENTINEL;
-    uint32_t ref_leaf_count = 0, fat_leaf_count = 0, wide_depth = 0, ref_depth = 0;
+    uint32_t ref_leaf_count = 0, fat_leaf_count = 0, wide_depth = 0, ref_depth = 0, twin_pair_count = 0;
 };
 
 // Returns 0, or a negative RT_E_* (include/b200rt.h).
@@ -84,5 +88,5 @@ struct RtAccel
 {
     AccelView view{};
     uint64_t device_bytes = 0;
-    uint32_t wide_count = 0, slot_count = 0, ref_leaf_count = 0, fat_leaf_count = 0, wide_depth = 0, ref_depth = 0;
+    uint32_t wide_count = 0, slot_count = 0, ref_leaf_count = 0, fat_leaf_count = 0, wide_depth = 0, ref_depth = 0, twin_pair_count = 0;
 };

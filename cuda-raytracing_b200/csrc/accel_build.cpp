@@ -50,6 +50,7 @@ namespace
         std::vector<Box> slot_box;      // per slot, for sub-trees
         std::vector<float> slot_centroid;
         int error = 0;
+        bool pair_twins = true;
 
         Box SlotBox(uint32_t s) const
         {
@@ -62,13 +63,39 @@ namespace
             return b;
         }
 
+        // Inside one product leaf [first, first+count): move every face next to its duplicate (bit-equal v0, e1/e2 exchanged:
+        // what Scene::AddLoadedScene's smooth face + AddTriangle flat copy produce, Scene.cpp:110-127) and flag the first of the
+        // pair (RT_TWIN_BIT). Slot order inside a leaf is free: the hit rule is order-independent and exact ties are resolved by
+        // orig_slot / face id, which travel with the record.
+        static bool IsTwin(const TriRecord& a, const TriRecord& b)
+        {
+            return std::memcmp(a.v0, b.v0, 12) == 0 && std::memcmp(a.e1, b.e2, 12) == 0 && std::memcmp(a.e2, b.e1, 12) == 0;
+        }
+        uint32_t LeafWithTwins(uint32_t first, uint32_t count)
+        {
+            if (pair_twins)
+                for (uint32_t i = first; i + 1 < first + count; i++)
+                {
+                    for (uint32_t j = i + 1; j < first + count; j++)
+                        if (IsTwin(out.tris[i], out.tris[j]))
+                        {
+                            std::swap(out.tris[i + 1], out.tris[j]); std::swap(out.shade[i + 1], out.shade[j]);
+                            out.tris[i].ref_leaf |= RT_TWIN_BIT;
+                            out.twin_pair_count++;
+                            i++;  // the copy itself starts no pair
+                            break;
+                        }
+                }
+            return LeafRef(first, count);
+        }
+
         // SAH sweep sub-tree over slots [first, first+count); permutes tris/shade inside the range.
         uint32_t BuildSub(uint32_t first, uint32_t count, uint32_t depth, Box& bounds_out)
         {
             Box bounds = EmptyBox();
             for (uint32_t s = first; s < first + count; s++) Grow(bounds, SlotBox(s));
             bounds_out = bounds;
-            if (count <= 4) return LeafRef(first, count);
+            if (count <= 4) return LeafWithTwins(first, count);
 
             std::vector<uint32_t> order(count);
             std::vector<Box> boxes(count);
@@ -127,7 +154,7 @@ namespace
                 out.ref_leaf_count++;
                 if ((uint64_t)node.first_index + node.prim_count > out.tris.size()) { error = RT_E_INVALID; return RT_SENTINEL; }
                 for (uint32_t s = node.first_index; s < node.first_index + node.prim_count; s++) out.tris[s].ref_leaf = n;
-                if (node.prim_count <= threshold) return LeafRef(node.first_index, node.prim_count);
+                if (node.prim_count <= threshold) return LeafWithTwins(node.first_index, node.prim_count);
                 out.fat_leaf_count++;
                 Box unused;
                 return BuildSub(node.first_index, node.prim_count, depth, unused);
@@ -183,7 +210,7 @@ int BuildAccelHost(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* 
     }
     if (invalid) return RT_E_INVALID;
     lap("gather records");
-    Builder builder{ nodes, node_count, fat_leaf_threshold, out, {}, {}, 0 };
+    Builder builder{ nodes, node_count, fat_leaf_threshold, out, {}, {}, 0, std::getenv("B200RT_NO_TWINS") == nullptr };
     out.wide.reserve(node_count / 2 + 16);
     out.root_ref = builder.Emit(0, 0);
     lap("wide nodes");

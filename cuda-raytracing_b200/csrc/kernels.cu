@@ -232,7 +232,7 @@ __device__ __forceinline__ void extend_leaf(const AccelView& A, uint32_t leaf, E
         const uint32_t id = __float_as_uint(r0.w);
         const uint32_t key = kTieById ? id : __float_as_uint(r2.w);
         if (!accept(t, key, L.h)) continue;
-        const uint32_t ref_leaf = __float_as_uint(r1.w);
+        const uint32_t ref_leaf = __float_as_uint(r1.w) & RT_REF_LEAF_MASK;
         if (ref_leaf != L.verified_leaf)
         {
             if (!exact_box(L.o, L.d, A.ref_nodes + ref_leaf, L.start_length)) continue;

@@ -212,7 +212,7 @@ __global__ void __launch_bounds__(256, kMinBlocks) pathtrace_regroup_kernel(Acce
         if (trav && node == RT_SENTINEL)
         {   // ray finished: the reference only counts a triangle whose leaf box passes (main_raytracing.cu:46) - checked once, on the
             // winner; if it fails (grazing within rounding, rare) the ray is redone with the per-candidate check
-            if (h.id != RT_MISS_ID && !(h.id & RT_SPHERE_ID_BIT) && !exact_box(ps.o, ps.d, A.ref_nodes + __ldg(&A.tris[h.slot].ref_leaf), start_length))
+            if (h.id != RT_MISS_ID && !(h.id & RT_SPHERE_ID_BIT) && !exact_box(ps.o, ps.d, A.ref_nodes + (__ldg(&A.tris[h.slot].ref_leaf) & RT_REF_LEAF_MASK), start_length))
             {
                 h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
                 sphere_tests(S.spheres, S.sphere_count, ps.o, nd, h);

@@ -68,8 +68,21 @@ __device__ __forceinline__ bool exact_box(Vec3 o, Vec3 d, const RtBVHNode* node,
 // itself out of the traversal loop's live set). Every intermediate is then the exact negation of GLM's (IEEE negation is exact
 // and round-to-nearest is symmetric: fl(-a + b) = -fl(a - b), fl((-a) * b) = -fl(a * b)), the comparisons are mirrored, and the
 // results are negated back: bit-identical t, u, v.
+//
+// twin_clear_miss (optional): every imported mesh face exists twice in the reference's scene (Scene.cpp:110-127: the smooth
+// indexed face, then AddTriangle's flat copy with v1/v2 exchanged), and both copies always fall into the same leaf (same centroid).
+// The copy's test is the SAME three scalar triple products with e1/e2 exchanged (det' = -det, u' = -v, v' = -u in exact
+// arithmetic, on bit-identical inputs dist/nd/e1/e2), so when this record misses by more than the rounding error of both
+// evaluations the copy misses too and need not be fetched. Rounding bound: a computed triple product c.(a x b) of fp32 vectors is
+// within 30 eps |a|inf |b|inf |c|inf of the exact one (two roundings per cross component, three products + two sums in the dot),
+// i.e. E <= 30 eps M (Tm + M) with M = max(|e1|inf, |e2|inf), Tm = |dist|inf, |nd|inf <= 1, eps = 2^-24. The copy is proven to
+// miss when a range test fails by delta > 7 E (3 E for this evaluation's u, v, det, 3 E for the copy's, 1 E for the two u + v
+// roundings) and |det| > delta + FLT_EPSILON (so the copy takes the opposite-sign branch); delta = 2^-14 M (Tm + M) = 1024 eps M (Tm + M)
+// is five times that. Only rays within ~1 % of an edge (in barycentric units at the bunny's scale) are "not clear"; those fetch and
+// test the copy as before, so results stay bit-identical (tests/test_gpu_parity.py).
 template <bool kNegO = false>
-__device__ __forceinline__ bool tri_test(Vec3 o, Vec3 nd, float4 r0, float4 r1, float4 r2, float& t, float& bu, float& bv)
+__device__ __forceinline__ bool tri_test(Vec3 o, Vec3 nd, float4 r0, float4 r1, float4 r2, float& t, float& bu, float& bv,
+                                         bool* twin_clear_miss = nullptr)
 {
     const Vec3 v0 = mk3(r0.x, r0.y, r0.z), e1 = mk3(r1.x, r1.y, r1.z), e2 = mk3(r2.x, r2.y, r2.z);
     const Vec3 p = cross3(nd, e2);
@@ -80,17 +93,24 @@ __device__ __forceinline__ bool tri_test(Vec3 o, Vec3 nd, float4 r0, float4 r1, 
         const float u = dot3(dist, p);
         const Vec3 perp = cross3(dist, e1);
         const float v = dot3(nd, perp);
-        if (det > FLT_EPSILON)
-        {
-            if (u < 0.0f || u > det) return false;
-            if (v < 0.0f || (u + v) > det) return false;
-        }
-        else if (det < -FLT_EPSILON)
-        {
-            if (u > 0.0f || u < det) return false;
-            if (v > 0.0f || (u + v) < det) return false;
-        }
+        const bool want_twin = twin_clear_miss && *twin_clear_miss;  // in: this record's copy sits in the next slot
+        if (twin_clear_miss) *twin_clear_miss = false;               // out: the copy provably misses as well
+        bool miss;
+        if (det > FLT_EPSILON) miss = (u < 0.0f || u > det) || (v < 0.0f || (u + v) > det);
+        else if (det < -FLT_EPSILON) miss = (u > 0.0f || u < det) || (v > 0.0f || (u + v) < det);
         else return false;
+        if (miss)
+        {
+            if (want_twin)
+            {
+                const float M = fmaxf(fmaxf(fmaxf(fabsf(e1.x), fabsf(e1.y)), fmaxf(fabsf(e1.z), fabsf(e2.x))), fmaxf(fabsf(e2.y), fabsf(e2.z)));
+                const float Tm = fmaxf(fmaxf(fabsf(dist.x), fabsf(dist.y)), fabsf(dist.z));
+                const float delta = (M * 6.103515625e-5f) * (Tm + M);
+                const float ad = fabsf(det), us = det > 0.0f ? u : -u, vs = det > 0.0f ? v : -v;
+                *twin_clear_miss = ad > delta + FLT_EPSILON && (fminf(us, vs) < -delta || fmaxf(us, us + vs) > ad + delta);
+            }
+            return false;
+        }
         const float inv_det = 1.0f / det;
         t = dot3(e2, perp) * inv_det;
         bu = u * inv_det; bv = v * inv_det;
@@ -139,18 +159,19 @@ static __device__ unsigned long long g_tw_hist[66];  // [n] iterations with n la
 
 template <bool kLazyExactBox, bool kTieById, bool kNegO = false>
 __device__ __forceinline__ void leaf_test_one(const AccelView& A, float4 r0, float4 r1, float4 r2, uint32_t slot, Vec3 o, Vec3 d, Vec3 nd,
-                                              float start_length, HitRecord& h, uint32_t* verified_leaf = nullptr)
+                                              float start_length, HitRecord& h, uint32_t* verified_leaf = nullptr, bool* twin_clear_miss = nullptr)
 {
     static_assert(!(kLazyExactBox && kNegO), "the per-candidate leaf-box check needs the origin itself");
     float t, bu, bv;
-    if (!tri_test<kNegO>(o, nd, r0, r1, r2, t, bu, bv)) return;
+    if (twin_clear_miss) *twin_clear_miss = (__float_as_uint(r1.w) & RT_TWIN_BIT) != 0u;
+    if (!tri_test<kNegO>(o, nd, r0, r1, r2, t, bu, bv, twin_clear_miss)) return;
     const uint32_t id = __float_as_uint(r0.w);
     const uint32_t key = kTieById ? id : __float_as_uint(r2.w);
     if (!accept(t, key, h)) return;
     if (kLazyExactBox)
     {   // the reference only tests this triangle if its leaf's box passes (main_raytracing.cu:46); optional one-entry cache of
         // the last leaf that passed (the smooth/flat duplicates of a face share a leaf and are accepted back to back)
-        const uint32_t leaf = __float_as_uint(r1.w);
+        const uint32_t leaf = __float_as_uint(r1.w) & RT_REF_LEAF_MASK;
         if (!verified_leaf || *verified_leaf != leaf)
         {
             if (!exact_box(o, d, A.ref_nodes + leaf, start_length)) return;
@@ -242,6 +263,9 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
 #endif
 #ifndef RT_TW_MODE
 #define RT_TW_MODE 7
+#endif
+#ifndef RT_TW_TWIN
+#define RT_TW_TWIN 0   /* mode 7: skip the duplicate of a mesh face when the first copy misses by a proven margin (tri_test): bit-identical, measured slower (57.9 vs 56.3 ms), off */
 #endif
 
 //   kDeferred (template): the exact reference-leaf box re-check (6 IEEE divisions, ~110 instructions, executed by the ~2 lanes
@@ -485,7 +509,20 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
         {
             if (RT_TW_PARK && kDeferred) leaf_test_one_parked<kTieById>(q0, q1, q2, slot, o, nd, h.t, park, park_stride);
             else if (RT_TW_NEGO && kDeferred) leaf_test_one<false, kTieById, true>(A, q0, q1, q2, slot, mk3(no_xy.x, no_xy.y, no_zz.x), d, nd, start_length, h, verified_ptr);
+#if RT_TW_TWIN
+            else
+            {   // a record whose copy (Scene.cpp:110-127) is the next slot of this leaf and provably misses too: skip the copy
+                bool skip_twin;
+                leaf_test_one<!kDeferred, kTieById>(A, q0, q1, q2, slot, o, d, nd, start_length, h, verified_ptr, &skip_twin);
+                tcut = h.t * kBestWiden;
+                const uint32_t step = skip_twin ? 2u : 1u;
+                if (((node >> 27) & 0xFu) >= step) node = node - (step << 27) + step;
+                else RT_POP();
+                continue;
+            }
+#else
             else leaf_test_one<!kDeferred, kTieById>(A, q0, q1, q2, slot, o, d, nd, start_length, h, verified_ptr);
+#endif
             tcut = h.t * kBestWiden;
             if (node & 0x78000000u) node = node - (1u << 27) + 1u;
             else RT_POP();
@@ -593,7 +630,7 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
 #undef RT_POP
     if (kDeferred && h.id != RT_MISS_ID && !(h.id & RT_SPHERE_ID_BIT))
     {   // h entered as a sphere hit or a miss, so a triangle id means "found here": verify its reference leaf (main_raytracing.cu:46)
-        const uint32_t leaf = __ldg(&A.tris[h.slot].ref_leaf);
+        const uint32_t leaf = __ldg(&A.tris[h.slot].ref_leaf) & RT_REF_LEAF_MASK;
 #ifdef RT_TW_FORCE_REDO
         if ((h.slot & RT_TW_FORCE_REDO) == 0u) return false;  // test hook: exercise the redo path on a fraction of the rays
 #endif

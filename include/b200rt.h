@@ -67,7 +67,8 @@ int rt_accel_create(const RtBVHNode* nodes, uint32_t node_count, const uint32_t*
                     const RtFace* faces, uint32_t face_count, const RtVertex* vertices, uint32_t vertex_count,
                     uint32_t fat_leaf_threshold, RtAccel** out);
 int rt_accel_destroy(RtAccel* accel);
-/* info[0..7] = wide nodes, triangle slots, reference leaves, fat leaves, max depth (wide), device bytes lo, hi, reference depth */
+/* info[0..7] = wide nodes, triangle slots, reference leaves, fat leaves (low 32 bits) | adjacent duplicate-face pairs (high 32 bits),
+ * max depth (wide), device bytes lo, hi, reference depth */
 int rt_accel_info(const RtAccel* accel, uint64_t* info8);
 /* associate `accel` with scenes whose gpu_bvh_nodes == d_nodes_key (lookup used by raytracing_process) */
 int rt_accel_bind(const void* d_nodes_key, RtAccel* accel);

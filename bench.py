@@ -224,7 +224,7 @@ def run_b200_arm(a):
         for i, s in enumerate(spp_launch):
             process_ex(surface, d.last, W, H, d.pitch, i if blend == 0 else 0, d.gpu, d.accel, spp=s, bounces=a.bounces,
                        blend_mode=blend, variant=variant, write_last=1 if blend == 0 else 0, ray_counter=d.counter,
-                       stream=stream, work_counters=work)
+                       stream=stream, work_counters=work, workspace=d.workspace)
 
     # ---- algorithmic bytes per ray: reference-order work counters on this exact workload (2 spp is plenty) ----
     work = torch.zeros(2, dtype=torch.int64, device=dev)

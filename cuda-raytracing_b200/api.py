@@ -220,7 +220,14 @@ class Tracer:
 
 
 def process_ex(surface, last, width, height, pitch, frame_index, scene_ptr, accel_ptr, spp=5, bounces=6, blend_mode=0,
-               variant=0, write_last=0, ray_counter=None, stream=None, work_counters=None):
+               variant=0, write_last=0, ray_counter=None, stream=None, work_counters=None, workspace=None):
+    """workspace: zero-filled uint8 device tensor of process_workspace_bytes(width, height) (cost-ordered tile scheduling
+    state kept between launches), or None = grid order."""
+    ws_bytes = int(workspace.numel() * workspace.element_size()) if workspace is not None else 0
     p = ProcessParams(ptr(surface), ptr(last), width, height, pitch, frame_index, spp, bounces, blend_mode, variant,
-                      write_last, scene_ptr, accel_ptr, ptr(ray_counter), ptr(stream), None, 0, ptr(work_counters))
+                      write_last, scene_ptr, accel_ptr, ptr(ray_counter), ptr(stream), ptr(workspace), ws_bytes, ptr(work_counters))
     check(lib().rt_process_ex(C.byref(p)))
+
+
+def process_workspace_bytes(width, height, variant=0):
+    return int(lib().rt_process_workspace_bytes(width, height, variant))

@@ -170,8 +170,7 @@ int rt_count_reference_work(const RtAccel* accel, const RtGPUScene* scene, int w
 // ---- path tracing ---------------------------------------------------------------------------
 uint64_t rt_process_workspace_bytes(int width, int height, int variant)
 {
-    (void)width; (void)height;
-    return variant == 0 ? 0 : 0;
+    return variant == 0 && width > 0 && height > 0 ? PathTraceWorkspaceBytes(width, height) : 0;
 }
 
 int rt_process_ex(const RtProcessParams* p)

@@ -35,6 +35,7 @@ cudaError_t LaunchCountWork(const AccelView& accel, const SceneView& scene, int 
                             uint32_t* d_counts, cudaStream_t stream);
 
 cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, const RtProcessParams& p, cudaStream_t stream);
+uint64_t PathTraceWorkspaceBytes(int width, int height);  // cost-ordered tile scheduling state (pathtrace.cu), zero-filled by the caller
 // variant 1: regrouping persistent kernel (pathtrace_regroup.cu); d_pixel_counter = one device uint owned by the caller for this launch
 cudaError_t LaunchPathTraceRegroup(const AccelView& accel, const SceneView& scene, const RtProcessParams& p, unsigned int* d_pixel_counter,
                                    cudaStream_t stream);

@@ -21,12 +21,14 @@ namespace RayTracing
     {
         if (rng_state) cudaFree(rng_state);
         if (d_ray_counter) cudaFree(d_ray_counter);
+        if (tile_workspace) cudaFree(tile_workspace);
     }
 
     void CUDARayTracer::OnResize(SurfaceData surface_)  // RayTracing.cpp:72-77
     {
         surface = surface_;
         if (rng_state) { cudaFree(rng_state); rng_state = nullptr; }
+        if (tile_workspace) { cudaFree(tile_workspace); tile_workspace = nullptr; tile_workspace_bytes = 0; }
         scene->AddDirtyFlag(DirtyFlagValue::Samples);
     }
 
@@ -53,6 +55,16 @@ namespace RayTracing
             cudaMemset(d_ray_counter, 0, sizeof(unsigned long long));
         }
 
+        if (!tile_workspace)
+        {   // per-tile cost of the previous frame -> heaviest-first tile order of the next one (csrc/pathtrace.cu); zero = no history
+            tile_workspace_bytes = rt_process_workspace_bytes((int)surface.width, (int)surface.height, 0);
+            if (tile_workspace_bytes)
+            {
+                if (cudaMalloc(&tile_workspace, tile_workspace_bytes) != cudaSuccess) throw std::runtime_error("allocation failed");
+                cudaMemset(tile_workspace, 0, tile_workspace_bytes);
+            }
+        }
+
         scene->GetCamera().SetViewportSize(vec2((float)surface.width, (float)surface.height));  // :223
         scene->Update(0.0f);                                                                   // :224
         if (scene->IsFlagDirty(DirtyFlagValue::Samples)) frame_index = 0;                       // :226-229
@@ -66,6 +78,7 @@ namespace RayTracing
         p.frame_index = frame_index; p.samples_per_launch = options.samples_per_launch; p.max_bounces = options.max_bounces;
         p.blend_mode = 0; p.variant = options.kernel_variant; p.write_last_frame = 1;
         p.scene = scene.get(); p.accel = scene->GetAccel(); p.d_ray_counter = d_ray_counter; p.stream = nullptr;
+        p.workspace = tile_workspace; p.workspace_bytes = tile_workspace_bytes;
         if (rt_process_ex(&p) != RT_OK) throw std::runtime_error(rt_last_error());
         frame_index++;                                                                          // :234
     }

@@ -61,6 +61,8 @@ namespace RayTracing
         std::unique_ptr<Scene> scene;
         RtRngState* rng_state = nullptr;  // device, 48 B x ceil(W*H/128)*128
         unsigned long long* d_ray_counter = nullptr;
+        void* tile_workspace = nullptr;   // device: tile order + per-tile cost (rt_process_workspace_bytes), reset on resize
+        uint64_t tile_workspace_bytes = 0;
         SurfaceData surface;
     };
 }

@@ -30,6 +30,8 @@ class DeviceScene:
         self.surface.view(torch.uint8).fill_(1)
         self.last = torch.zeros((height, width, 4), dtype=torch.float32, device=device)
         self.counter = torch.zeros(1, dtype=torch.int64, device=device)
+        from cuda_raytracing_b200.api import process_workspace_bytes
+        self.workspace = torch.zeros(max(process_workspace_bytes(width, height), 4), dtype=torch.uint8, device=device)
         self.set_pose(pose)
 
     def reseed(self, seed, first_subsequence=0):
@@ -68,11 +70,11 @@ class DeviceScene:
         t.cuda.synchronize()
         return ids.cpu().numpy().view(np.uint32)[:n], ts.cpu().numpy()[:n]
 
-    def process(self, frame_index, spp=5, bounces=6, blend_mode=0, variant=0, write_last=0, surface=None, last=None):
+    def process(self, frame_index, spp=5, bounces=6, blend_mode=0, variant=0, write_last=0, surface=None, last=None, ordered=True):
         from cuda_raytracing_b200.api import process_ex
         process_ex(self.surface if surface is None else surface, self.last if last is None else last, self.width, self.height,
                    self.pitch, frame_index, self.gpu, self.accel, spp=spp, bounces=bounces, blend_mode=blend_mode, variant=variant,
-                   write_last=write_last, ray_counter=self.counter)
+                   write_last=write_last, ray_counter=self.counter, workspace=self.workspace if ordered else None)
 
     def rays(self):
         self.torch.cuda.synchronize()

@@ -8,12 +8,16 @@
 //   (SIMT efficiency no longer limited by the longest path per sample). Per pixel the order of RNG
 //   draws and fp32 operations is the reference's, so the stream and the image are reproduced.
 //   The XORWOW state lives in registers for the launch (reference: 24-B global RMW per draw).
+#include <algorithm>
 #include <cmath>
 #include <cstdlib>
 #include "shade.cuh"
 
 #ifndef RT_PT_BLOCK
 #define RT_PT_BLOCK 128  // threads per CTA of the megakernel: 256 / 128 / 64 = 57.0 / 56.0 / 56.8 ms (finer-grained tail of the last wave)
+#endif
+#ifndef RT_PT_BINNING
+#define RT_PT_BINNING 0  // 1: measurement build of the cost-binned pixel -> lane experiment (slower the more global the binning: off)
 #endif
 #ifndef RT_PT_FMA
 #define RT_PT_FMA 0  // 1: slab test of the path tracer in FMA form (traverse.cuh, kFma): 1 % faster on the bunny, 1.9x slower on config 4b
@@ -34,6 +38,8 @@ struct FrameParams
     int width, height;
     uint64_t pitch;
     int frame_index, spp, max_bounces, blend_mode, write_last, row_order;
+    const uint32_t* pixel_perm;  // experiment: pixel handled by thread k of (virtual) tile t = pixel_perm[t * RT_PT_BLOCK + k], ~0u = none
+    uint32_t* pixel_cost;        // experiment (kCount): traversal steps this launch spent on each pixel
     const uint32_t* tile_order;  // cost-ordered scheduling (workspace): tile processed by the k-th CTA, or nullptr = grid order
     uint32_t* tile_cost;         // per tile: SM cycles / 16 its slowest warp took in this launch (input of the next launch's order)
     unsigned long long* ray_counter;
@@ -65,7 +71,7 @@ __device__ __forceinline__ void write_pixel(const FrameParams& P, int x, int y, 
 
 // kMode 0: product traversal. kMode 2: reference-order traversal with work counters (measurement of the
 // algorithmic bytes per ray; same image up to exact-tie resolution).
-template <int kMode, int kMinBlocks, bool kLockstep = false>
+template <int kMode, int kMinBlocks, bool kLockstep = false, bool kCount = false>
 __global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK)) pathtrace_megakernel(AccelView A, SceneView S, FrameParams P)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -82,9 +88,16 @@ __global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK))
         bx = tile % tiles_x; by = tile / tiles_x;
         t_start = clock64();
     }
-    const int x = bx * 16 + (warp & 1) * 8 + (lane & 7);
-    const int y = by * (RT_PT_BLOCK / 16) + (warp >> 1) * 4 + (lane >> 3);
-    const bool active = x < P.width && y < P.height;
+    int x = bx * 16 + (warp & 1) * 8 + (lane & 7);
+    int y = by * (RT_PT_BLOCK / 16) + (warp >> 1) * 4 + (lane >> 3);
+    bool active = x < P.width && y < P.height;
+    if (RT_PT_BINNING && P.pixel_perm)
+    {
+        const uint32_t pix = __ldg(P.pixel_perm + (size_t)(P.tile_order ? tile : blockIdx.x) * RT_PT_BLOCK + threadIdx.x);
+        active = pix != 0xFFFFFFFFu;
+        x = (int)(pix % (uint32_t)P.width); y = (int)(pix / (uint32_t)P.width);
+    }
+    uint32_t steps = 0;
     unsigned rays = 0;
     uint32_t work_nodes = 0, work_tris = 0;
     const unsigned lane_mask = __ballot_sync(0xffffffffu, active);
@@ -119,7 +132,7 @@ __global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK))
                 sphere_tests(S.spheres, S.sphere_count, ps.o, nd, r);
             };
             HitRecord h; reinit(h);
-            if (kMode == 0) trace_wide<false, RT_PT_FMA != 0>(A, ps.o, ps.d, nd, h, reinit);
+            if (kMode == 0) trace_wide<false, RT_PT_FMA != 0>(A, ps.o, ps.d, nd, h, reinit, kCount ? &steps : nullptr);
             else trace_reference_order<false>(A, ps.o, ps.d, nd, h, &work_nodes, &work_tris);
             rays++;
             bool alive;
@@ -129,6 +142,7 @@ __global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK))
         }
         rng.store(state);
         write_pixel(P, x, y, sum);
+        if (RT_PT_BINNING && kCount && P.pixel_cost) P.pixel_cost[(size_t)y * P.width + x] = steps;
     }
     if (P.tile_order && lane == 0)
     {
@@ -202,9 +216,17 @@ __global__ void __launch_bounds__(1024) tile_order_kernel(uint32_t* ws, uint32_t
     if (threadIdx.x == 0) ws[3]++;
 }
 
+#if RT_PT_BINNING
+// measurement build only (benchmarks/pixel_binning.py): explicit pixel -> lane assignment and a per-pixel step count
+static const uint32_t* g_debug_pixel_perm = nullptr;
+static uint32_t* g_debug_pixel_cost = nullptr;
+extern "C" void rt_debug_pixel_binning(const uint32_t* d_perm, uint32_t* d_cost) { g_debug_pixel_perm = d_perm; g_debug_pixel_cost = d_cost; }
+#endif
+
 uint64_t PathTraceWorkspaceBytes(int width, int height)
 {
-    const uint64_t n = (uint64_t)((width + 15) / 16) * (uint64_t)((height + RT_PT_BLOCK / 16 - 1) / (RT_PT_BLOCK / 16));
+    uint64_t n = (uint64_t)((width + 15) / 16) * (uint64_t)((height + RT_PT_BLOCK / 16 - 1) / (RT_PT_BLOCK / 16));
+    n = std::max<uint64_t>(n, ((uint64_t)width * height + RT_PT_BLOCK - 1) / RT_PT_BLOCK);
     return (RT_TILE_HDR + 2 * n) * sizeof(uint32_t);
 }
 
@@ -235,11 +257,17 @@ cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, cons
     }
     dim3 grid((p.width + 15) / 16, (p.height + tile_h - 1) / tile_h), block(RT_PT_BLOCK);
     P.tile_order = nullptr; P.tile_cost = nullptr;
+    P.pixel_perm = nullptr; P.pixel_cost = nullptr;
+#if RT_PT_BINNING
+    P.pixel_perm = g_debug_pixel_perm; P.pixel_cost = g_debug_pixel_cost;
+#endif
+    if (P.pixel_perm) grid = dim3((unsigned)(((size_t)p.width * p.height + RT_PT_BLOCK - 1) / RT_PT_BLOCK), 1);
     static int use_order = -1;
     if (use_order < 0) { const char* v = getenv("B200RT_TILE_ORDER"); use_order = v ? atoi(v) : 1; }
     if (use_order && p.variant == 0 && p.workspace && p.workspace_bytes >= PathTraceWorkspaceBytes(p.width, p.height))
     {
         const uint32_t n = grid.x * grid.y;
+        if (P.pixel_perm && PathTraceWorkspaceBytes(p.width, p.height) < (RT_TILE_HDR + 2ull * n) * 4) return cudaErrorInvalidValue;
         uint32_t* ws = (uint32_t*)p.workspace;
         tile_order_kernel<<<1, 1024, 0, stream>>>(ws, (uint32_t)p.width, (uint32_t)p.height, n);
         P.tile_order = ws + RT_TILE_HDR; P.tile_cost = ws + RT_TILE_HDR + n;
@@ -248,6 +276,9 @@ cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, cons
     static int min_blocks = 0;
     if (!min_blocks) { const char* v = getenv("B200RT_MINBLOCKS"); min_blocks = v ? atoi(v) : 5; }  // occupancy sweep hook (profiles/)
     if (p.variant == 2) pathtrace_megakernel<2, 3><<<grid, block, 0, stream>>>(accel, scene, P);
+#if RT_PT_BINNING
+    else if (P.pixel_cost) pathtrace_megakernel<0, 5, false, true><<<grid, block, 0, stream>>>(accel, scene, P);
+#endif
     else if (min_blocks == 6) pathtrace_megakernel<0, 6><<<grid, block, 0, stream>>>(accel, scene, P);
     else if (min_blocks == 4) pathtrace_megakernel<0, 4><<<grid, block, 0, stream>>>(accel, scene, P);
     else if (min_blocks == 3) pathtrace_megakernel<0, 3><<<grid, block, 0, stream>>>(accel, scene, P);

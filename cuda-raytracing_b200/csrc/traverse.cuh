@@ -274,7 +274,7 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
 //     still found; if the WINNER's leaf box fails (a ray grazing a leaf box within rounding - rare) the function returns false
 //     and the caller redoes the ray with the per-candidate check (trace_wide below). Exact by construction.
 template <bool kTieById, bool kFma, bool kDeferred>
-__device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3 d, Vec3 nd, HitRecord& h)
+__device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3 d, Vec3 nd, HitRecord& h, uint32_t* steps = nullptr)
 {
     const float start_length = h.t;
     // reciprocal of the normalised direction; zero components -> huge finite (conservative)
@@ -492,6 +492,7 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
     // the memory latency of the node lanes and of the triangle lanes overlaps instead of adding up within an iteration.
     while (node != RT_SENTINEL)
     {
+        if (steps) (*steps)++;  // per-lane work measure (node + triangle steps) for cost-binned pixel scheduling
         const bool is_leaf = (node & RT_LEAF_BIT) != 0u;
         const uint32_t slot = node & 0x07FFFFFFu;
         const char* rec = is_leaf ? reinterpret_cast<const char*>(A.tris + slot) : reinterpret_cast<const char*>(A.wide + node);
@@ -647,10 +648,10 @@ __device__ __noinline__ void trace_wide_checked(const AccelView& A, Vec3 o, Vec3
 
 // `h` enters holding what reinit(h) produces (a miss, or the sphere result); reinit is only called again on the rare redo.
 template <bool kTieById, bool kFma = false, class Reinit>
-__device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, Vec3 nd, HitRecord& h, Reinit reinit)
+__device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, Vec3 nd, HitRecord& h, Reinit reinit, uint32_t* steps = nullptr)
 {
 #if RT_TW_DEFER
-    if (trace_wide_impl<kTieById, kFma, true>(A, o, d, nd, h)) return;
+    if (trace_wide_impl<kTieById, kFma, true>(A, o, d, nd, h, steps)) return;
     reinit(h);
     trace_wide_checked<kTieById, kFma>(A, o, d, nd, h);
 #else

@@ -78,6 +78,10 @@ SYMBOLS = {
     "rt_dds_read_level0": (_I, [C.c_char_p, _P, C.c_size_t]),
     "rt_trace_primary": (_I, [_P, _P, _I, _I, _I, _I, _P, _P, _P, _P]),
     "rt_trace_rays": (_I, [_P, _P, _P, _U64, _I, _I, _P, _P, _P, _P]),
+    "rt_texture_create_from_file": (_I, [C.c_char_p, _I, C.POINTER(_P)]),
+    "rt_texture_create_from_memory": (_I, [_P, C.c_size_t, _I, C.POINTER(_P)]),
+    "rt_texture_fetch": (_I, [_P, _I, _P, C.c_float, _P, _P]),
+    "rt_dds_info": (_I, [_P, C.c_size_t, C.POINTER(_U64), _I]),
     "rt_process_ex": (_I, [_P]),
     "rt_process_workspace_bytes": (_U64, [_I, _I, _I]),
     "rt_ambient_occlusion": (_I, [_P, _P, _I, _I, _I, _P, _P, _P]),

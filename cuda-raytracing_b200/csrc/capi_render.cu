@@ -11,6 +11,8 @@ struct RtEnvMap
 {
     cudaMipmappedArray_t array = nullptr;
     cudaTextureObject_t tex = 0;
+    int dims = 2;          // 1 / 2 / 3
+    bool is_cube = true;
 };
 
 namespace
@@ -60,6 +62,91 @@ namespace
         return RT_OK;
     }
 
+    // utils/CUDATexture.cpp:112-172 + :187-220 for every container / format the general parser accepts and CUDA has an array
+    // format for: 1D/2D, cubemap, 3D; plain, normalised and block-compressed texels; full mip chains.
+    // Differences from the reference, which never exercised these paths (its only texture is the RGBA32F cubemap):
+    //  * block-compressed arrays take TEXEL extents in cudaMallocMipmappedArray and cudaMemcpy3D (measured on the B200 box,
+    //    benchmarks/probe_bc.cu); the reference passes width/4 x height/4 and sizes the copy with 8+8+8+8 "bits per pixel", which
+    //    its own size check rejects for every BC format;
+    //  * a 2D texture is copied with depth 1 (the reference's TextureDesc::depth stays 0 for non-cubes, an empty copy);
+    //  * R16G16B16A16_UINT / _SINT are 4 x 16-bit channels (the reference maps them to uint4 / short2).
+    int CreateTexture(const uint8_t* bytes, const DdsImage& img, bool srgb, RtEnvMap** out)
+    {
+        const DxgiFormatInfo& f = img.format;
+        if (f.cuda_kind < 0) return Fail(RT_E_INVALID, std::string("DDS: no CUDA array format for DXGI ") + f.name);
+        const bool bc = f.block_bytes >= 8;
+        if (bc && ((img.width & 3u) || (img.height & 3u))) return Fail(RT_E_INVALID, "DDS: block-compressed size must be a multiple of 4");  // CUDATexture.cpp:122-124
+        if (img.is_cubemap ? (img.array_size != 6 || img.width != img.height) : (img.array_size != 1))
+            return Fail(RT_E_INVALID, "DDS: texture arrays (other than one cubemap) are parsed but have no texture path");
+        RtEnvMap* env = new RtEnvMap();
+        env->dims = img.num_dimensions; env->is_cube = img.is_cubemap;
+        const cudaChannelFormatDesc desc = cudaCreateChannelDesc(f.cx, f.cy, f.cz, f.cw, (cudaChannelFormatKind)f.cuda_kind);
+        const cudaExtent extent = img.is_cubemap ? make_cudaExtent(img.width, img.height, 6)
+                                : img.num_dimensions == 3 ? make_cudaExtent(img.width, img.height, img.depth)
+                                : make_cudaExtent(img.width, img.num_dimensions == 1 ? 0 : img.height, 0);
+        cudaError_t e = cudaMallocMipmappedArray(&env->array, &desc, extent, img.mip_count, img.is_cubemap ? cudaArrayCubemap : 0);
+        std::vector<uint8_t> staging;
+        for (uint32_t m = 0; e == cudaSuccess && m < img.mip_count; m++)
+        {
+            cudaArray_t level;
+            e = cudaGetMipmappedArrayLevel(&level, env->array, m);
+            if (e != cudaSuccess) break;
+            const DdsSubresource& s0 = img.subresources[m];
+            // mip-major re-pack: all array elements (cube faces) of this level back to back (CUDATexture.cpp:195-217)
+            const size_t element_bytes = s0.slice_pitch * s0.depth;
+            staging.resize(element_bytes * img.array_size);
+            for (uint32_t a = 0; a < img.array_size; a++)
+                memcpy(staging.data() + a * element_bytes, bytes + img.subresources[(size_t)a * img.mip_count + m].offset, element_bytes);
+            cudaMemcpy3DParms p = {};
+            const size_t rows = bc ? (s0.height + 3) / 4 : s0.height;  // rows of the source as laid out in memory
+            p.srcPtr = make_cudaPitchedPtr(staging.data(), s0.row_pitch, s0.width, rows);
+            p.dstArray = level;
+            p.extent = make_cudaExtent(s0.width, img.num_dimensions == 1 ? 1 : s0.height, img.is_cubemap ? 6 : s0.depth);
+            p.kind = cudaMemcpyHostToDevice;
+            if (bc)
+            {   // source rows are rows of 4x4 blocks: the pitched pointer describes texels, so its height is the texel height
+                p.srcPtr = make_cudaPitchedPtr(staging.data(), s0.row_pitch, s0.width < 4 ? 4 : s0.width, s0.height < 4 ? 4 : s0.height);
+                p.extent = make_cudaExtent(s0.width < 4 ? 4 : s0.width, s0.height < 4 ? 4 : s0.height, img.is_cubemap ? 6 : s0.depth);
+            }
+            e = cudaMemcpy3D(&p);
+        }
+        if (e == cudaSuccess)
+        {
+            cudaResourceDesc res; memset(&res, 0, sizeof(res));
+            res.resType = cudaResourceTypeMipmappedArray;
+            res.res.mipmap.mipmap = env->array;
+            cudaTextureDesc td; memset(&td, 0, sizeof(td));
+            td.normalizedCoords = 1;
+            const bool integer_texels = !f.normalized && f.cuda_kind != 2 && !bc;  // plain UINT / SINT: no filtering possible
+            td.filterMode = integer_texels ? cudaFilterModePoint : cudaFilterModeLinear;
+            td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeWrap;
+            td.readMode = f.normalized ? cudaReadModeNormalizedFloat : cudaReadModeElementType;
+            td.sRGB = srgb ? 1 : 0;
+            td.seamlessCubemap = img.is_cubemap ? 1 : 0;
+            td.maxMipmapLevelClamp = (float)(img.mip_count - 1);
+            e = cudaCreateTextureObject(&env->tex, &res, &td, nullptr);
+        }
+        if (e != cudaSuccess)
+        {
+            if (env->array) cudaFreeMipmappedArray(env->array);
+            delete env;
+            return CudaFail(e, "rt_texture_create");
+        }
+        *out = env;
+        return RT_OK;
+    }
+
+    // one texel fetch per thread: coords = 3 floats (direction for cubemaps; u, v, w otherwise)
+    __global__ void texture_fetch_kernel(cudaTextureObject_t tex, int dims, bool cube, int n, const float* __restrict__ coords, float lod, float4* __restrict__ out)
+    {
+        const int i = blockIdx.x * blockDim.x + threadIdx.x;
+        if (i >= n) return;
+        const float a = coords[3 * i], b = coords[3 * i + 1], c = coords[3 * i + 2];
+        out[i] = cube ? texCubemapLod<float4>(tex, a, b, c, lod)
+               : dims == 3 ? tex3DLod<float4>(tex, a, b, c, lod)
+               : dims == 1 ? tex1DLod<float4>(tex, a, lod) : tex2DLod<float4>(tex, a, b, lod);
+    }
+
     // Work counters of the persistent kernels: a ring of device words per device, one slot per launch (launches in flight on
     // different streams never share a slot unless more than kCounterSlots are outstanding).
     constexpr int kCounterSlots = 256;
@@ -94,9 +181,57 @@ extern "C" {
 int rt_envmap_create_from_memory(const void* dds_bytes, size_t size, RtEnvMap** out)
 {
     if (!dds_bytes || !out) return Fail(RT_E_INVALID, "rt_envmap_create_from_memory: null");
-    DdsCubemap dds; std::string err;
-    if (int r = ParseDdsCubemap(dds_bytes, size, dds, err)) return Fail(r, err);
-    return CreateEnvMap(dds, out);
+    DdsImage img; std::string err;
+    if (int r = ParseDds(dds_bytes, size, img, err)) return Fail(r, err);
+    if (!img.is_cubemap) return Fail(RT_E_IO, "DDS: not a six-face cubemap");
+    if (img.format.dxgi == 2 && img.array_size == 6)
+    {   // the asset's own layout (RGBA32F): the dedicated reader
+        DdsCubemap dds;
+        if (int r = ParseDdsCubemap(dds_bytes, size, dds, err)) return Fail(r, err);
+        return CreateEnvMap(dds, out);
+    }
+    return CreateTexture(static_cast<const uint8_t*>(dds_bytes), img, true, out);  // any other cubemap format CUDA can sample as float4
+}
+
+int rt_texture_create_from_memory(const void* dds_bytes, size_t size, int srgb, RtEnvMap** out)
+{
+    if (!dds_bytes || !out) return Fail(RT_E_INVALID, "rt_texture_create_from_memory: null");
+    DdsImage img; std::string err;
+    if (int r = ParseDds(dds_bytes, size, img, err)) return Fail(r, err);
+    return CreateTexture(static_cast<const uint8_t*>(dds_bytes), img, srgb != 0, out);
+}
+
+int rt_texture_create_from_file(const char* dds_path, int srgb, RtEnvMap** out)
+{
+    if (!dds_path || !out) return Fail(RT_E_INVALID, "rt_texture_create_from_file: null");
+    std::vector<uint8_t> bytes;
+    if (LoadFileBytes(dds_path, bytes)) return Fail(RT_E_IO, std::string("cannot read ") + dds_path);
+    return rt_texture_create_from_memory(bytes.data(), bytes.size(), srgb, out);
+}
+
+int rt_texture_fetch(const RtEnvMap* tex, int count, const float* d_coords, float lod, float* d_rgba, void* stream)
+{
+    if (!tex || !tex->tex || count < 0 || (count && (!d_coords || !d_rgba))) return Fail(RT_E_INVALID, "rt_texture_fetch: bad argument");
+    if (!count) return RT_OK;
+    texture_fetch_kernel<<<(count + 127) / 128, 128, 0, (cudaStream_t)stream>>>(tex->tex, tex->dims, tex->is_cube, count, d_coords, lod, (float4*)d_rgba);
+    RT_CUDA(cudaGetLastError());
+    return RT_OK;
+}
+
+int rt_dds_info(const void* dds_bytes, size_t size, uint64_t* info, int capacity)
+{
+    if (!dds_bytes || !info || capacity < 12) return Fail(RT_E_INVALID, "rt_dds_info: bad argument");
+    DdsImage img; std::string err;
+    if (int r = ParseDds(dds_bytes, size, img, err)) return Fail(r, err);
+    info[0] = img.width; info[1] = img.height; info[2] = img.depth; info[3] = img.mip_count; info[4] = img.array_size;
+    info[5] = img.is_cubemap; info[6] = (uint64_t)img.num_dimensions; info[7] = img.format.dxgi; info[8] = img.format.bits_per_pixel;
+    info[9] = img.format.block_bytes; info[10] = img.format.cuda_kind >= 0; info[11] = img.subresources.size();
+    const int n = (int)img.subresources.size();
+    for (int i = 0; i < n && 12 + 3 * i + 2 < capacity; i++)
+    {
+        info[12 + 3 * i] = img.subresources[i].offset; info[13 + 3 * i] = img.subresources[i].row_pitch; info[14 + 3 * i] = img.subresources[i].slice_pitch;
+    }
+    return n;
 }
 
 int rt_envmap_create_from_file(const char* dds_path, RtEnvMap** out)

@@ -264,6 +264,9 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
 #ifndef RT_TW_MODE
 #define RT_TW_MODE 7
 #endif
+#ifndef RT_TW_LEAN
+#define RT_TW_LEAN 0   /* mode 7, deferred: keep only (t, slot, key) of the best candidate in the loop; id, u, v are recomputed from the winner's record after it */
+#endif
 #ifndef RT_TW_TWIN
 #define RT_TW_TWIN 0   /* mode 7: skip the duplicate of a mesh face when the first copy misses by a proven margin (tri_test): bit-identical, measured slower (57.9 vs 56.3 ms), off */
 #endif
@@ -490,6 +493,9 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
     // mode 3 with ONE fetch for both kinds of step: every lane loads 56 bytes from its own record (a 64-byte wide node or a
     // 48-byte triangle record; the arrays are padded so the last triangle's +48 read stays inside) before the kinds diverge, so
     // the memory latency of the node lanes and of the triangle lanes overlaps instead of adding up within an iteration.
+#if RT_TW_LEAN
+    uint32_t win_slot = RT_SENTINEL, win_key = 0u;  // kDeferred only: the best TRIANGLE so far (h.t follows; id/slot/key/u/v of h stay the entry's until the end)
+#endif
     while (node != RT_SENTINEL)
     {
         if (steps) (*steps)++;  // per-lane work measure (node + triangle steps) for cost-binned pixel scheduling
@@ -508,6 +514,21 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
         if (!is_leaf) RT_NODE_MATH(q0, q1, q2, q3);
         else
         {
+#if RT_TW_LEAN
+            if (kDeferred)
+            {
+                float t, bu, bv;
+                const Vec3 oo = RT_TW_NEGO ? mk3(no_xy.x, no_xy.y, no_zz.x) : o;
+                if (tri_test<RT_TW_NEGO != 0>(oo, nd, q0, q1, q2, t, bu, bv) && !(t > h.t || t < 0.0f))
+                {
+                    const uint32_t key = kTieById ? __float_as_uint(q0.w) : __float_as_uint(q2.w);
+                    if (t < h.t || (win_slot != RT_SENTINEL && key < win_key)) { h.t = t; win_slot = slot; win_key = key; }
+                }
+                if (node & 0x78000000u) node = node - (1u << 27) + 1u;
+                else RT_POP();
+                continue;
+            }
+#endif
             if (RT_TW_PARK && kDeferred) leaf_test_one_parked<kTieById>(q0, q1, q2, slot, o, nd, h.t, park, park_stride);
             else if (RT_TW_NEGO && kDeferred) leaf_test_one<false, kTieById, true>(A, q0, q1, q2, slot, mk3(no_xy.x, no_xy.y, no_zz.x), d, nd, start_length, h, verified_ptr);
 #if RT_TW_TWIN
@@ -529,6 +550,16 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
             else RT_POP();
         }
     }
+#if RT_TW_LEAN
+    if (kDeferred && win_slot != RT_SENTINEL)
+    {   // the winner's details, once per ray: the same arithmetic on the same record gives the same t, u, v bit for bit
+        const char* rec = reinterpret_cast<const char*>(A.tris + win_slot);
+        const float4 q0 = ldg4(rec), q1 = ldg4(rec + 16), q2 = ldg4(rec + 32);
+        float t, bu, bv;
+        tri_test(o, nd, q0, q1, q2, t, bu, bv);
+        h.id = __float_as_uint(q0.w); h.slot = win_slot; h.key = win_key; h.bu = bu; h.bv = bv;
+    }
+#endif
     if (RT_TW_PARK && kDeferred)
     {
         h.id = park[0]; h.slot = park[park_stride]; h.key = park[2 * park_stride];

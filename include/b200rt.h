@@ -82,6 +82,18 @@ int rt_envmap_create_from_file(const char* dds_path, RtEnvMap** out);
 int rt_envmap_create_from_memory(const void* dds_bytes, size_t size, RtEnvMap** out);
 uint64_t rt_envmap_texture(const RtEnvMap* env);  /* cudaTextureObject_t */
 int rt_envmap_destroy(RtEnvMap* env);
+/* General DDS containers (utils/image/DDSLoader.cpp:135-371, utils/CUDATexture.cpp:9-75,187-220): legacy and DX10
+ * headers, 1D/2D/3D, cubemaps, mip chains, plain / normalised / block-compressed (BC1-BC7) texels -> mipmapped array + texture
+ * object (linear, wrap, normalised coordinates; seamless for cubemaps). rt_envmap_create_* accepts every CUBEMAP format of this
+ * path as the environment map (e.g. RGBA16F, BC6H). The handle type is shared with the environment map. */
+int rt_texture_create_from_file(const char* dds_path, int srgb, RtEnvMap** out);
+int rt_texture_create_from_memory(const void* dds_bytes, size_t size, int srgb, RtEnvMap** out);
+/* texel fetch probe: d_coords = 3 floats per sample (cubemap: direction; else u, v, w), d_rgba = 4 floats per sample */
+int rt_texture_fetch(const RtEnvMap* tex, int count, const float* d_coords, float lod, float* d_rgba, void* stream);
+/* host-side parse only (no device). info[0..11] = width, height, depth, mips, array size (x6 for cubemaps), is_cubemap, dimensions,
+ * DXGI format, bits per pixel, block bytes, has a CUDA array format, subresource count; then {offset, row pitch, slice pitch} per
+ * subresource in file order (array element major) while they fit `capacity`. Returns the subresource count or < 0. */
+int rt_dds_info(const void* dds_bytes, size_t size, uint64_t* info, int capacity);
 /* host-side parse only (no device): level-0 texels [6][size][size][4] floats; returns size or <0 */
 int rt_dds_read_level0(const char* dds_path, float* out_texels, size_t capacity_floats);
 

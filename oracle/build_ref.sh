@@ -36,7 +36,12 @@ sed -e 's/raytracing_kernel_main<<<Dg, Db>>>(render_data);/(void)Dg; (void)rende
 grep -q refbench_bounces "$OUT/rt_bench.inc" && grep -q refbench_spp "$OUT/rt_bench.inc" && grep -q 'refbench_rays++' "$OUT/rt_bench.inc"
 g++ ${CXXFLAGS/-O2/-O3} $INC -I"$R/RayTracing" -DRT_BENCH_SRC="\"$OUT/rt_bench.inc\"" \
     -c "$HERE/ref_shim/ref_bench.cpp" -o "$OUT/ref_bench.o"
-g++ -shared -fopenmp -o "$OUT/libref_oracle.so" "$OUT/ref_api.o" "$OUT/ref_bench.o" "$OUT/bvh_ref.o"
+# the reference's DDS container parser, verbatim TU + a Windows.h stand-in (types / SAL / HRESULT names only): pins csrc/dds.cpp ParseDds
+g++ $CXXFLAGS '-D__declspec(x)=__attribute__((weak))' -include "$HERE/ref_shim/winshim/Windows.h" -I"$HERE/ref_shim/winshim" -I"$R" -I"$R/utils/image" \
+    -c "$R/utils/image/DDSLoader.cpp" -o "$OUT/dds_ref.o"
+g++ $CXXFLAGS '-D__declspec(x)=__attribute__((weak))' -include "$HERE/ref_shim/winshim/Windows.h" -I"$HERE/ref_shim/winshim" -I"$R" -I"$R/utils/image" \
+    -c "$HERE/ref_shim/ref_dds.cpp" -o "$OUT/ref_dds.o"
+g++ -shared -fopenmp -o "$OUT/libref_oracle.so" "$OUT/ref_api.o" "$OUT/ref_bench.o" "$OUT/bvh_ref.o" "$OUT/dds_ref.o" "$OUT/ref_dds.o"
 rm -f "$OUT/rt_host.inc" "$OUT/rt_bench.inc" "$OUT"/*.o
 echo "built $OUT/libref_oracle.so"
 # The reference's own CUDA kernels, UNMODIFIED, for sm_100a (BASELINE.json: "where the reference's own CUDA kernel builds

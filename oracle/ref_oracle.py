@@ -42,8 +42,17 @@ def lib():
         h.ref_render_frame.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
                                        C.c_uint32, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                        C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_int, C.c_int]
+        h.ref_dds_info.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_int]; h.ref_dds_info.restype = C.c_int
         _lib = h
     return _lib
+
+
+def dds_info(data, capacity=12 + 3 * 256):
+    """The reference's own GetDDSSubresources on a DDS file image: (subresource count or < 0, info array) - layout of rt_dds_info."""
+    buf = np.frombuffer(bytes(data), np.uint8).copy()
+    info = np.zeros(capacity, np.uint64)
+    n = lib().ref_dds_info(_p(buf), len(buf), _p(info), capacity)
+    return n, info
 
 
 def _p(a):

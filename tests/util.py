@@ -69,3 +69,45 @@ def bunny_scene(rt, env=False):
 def raw(a):
     """uint8 [n, itemsize] view of a structured array (what oracle/ref_oracle.py takes)."""
     return np.ascontiguousarray(a).view(np.uint8).reshape(len(a), -1)
+
+
+# ---- DDS containers for the general loader tests (SURVEY 8f.3) ------------------------------------------------------------
+DDSD = {"caps": 0x1, "height": 0x2, "width": 0x4, "pitch": 0x8, "pixelformat": 0x1000, "mips": 0x20000, "linear": 0x80000, "depth": 0x800000}
+
+
+def fourcc(s):
+    return struct.unpack("<I", s.encode("ascii"))[0]
+
+
+def make_dds(width, height, payload, pixel_format=None, dxgi=None, depth=0, mips=1, cube=False, array=1, dimension=3, volume=False,
+             caps2=None, mip_field=None):
+    """A DDS file image. pixel_format = (flags, fourCC, bits, R, G, B, A) for a legacy header, or dxgi = DXGI_FORMAT for a DX10 one."""
+    flags = DDSD["caps"] | DDSD["height"] | DDSD["width"] | DDSD["pixelformat"] | (DDSD["mips"] if mips > 1 else 0) | (DDSD["depth"] if volume else 0)
+    if dxgi is not None:
+        pixel_format = (0x4, fourcc("DX10"), 0, 0, 0, 0, 0)
+    header = struct.pack("<7I", 124, flags, height, width, 0, depth, mips if mip_field is None else mip_field) + b"\0" * 44
+    header += struct.pack("<8I", 32, *pixel_format)
+    if caps2 is None:
+        caps2 = (0xFE00 if cube and dxgi is None else 0) | (0x200000 if volume else 0)
+    header += struct.pack("<5I", 0x1000 | (0x8 if cube or mips > 1 else 0) | (0x400000 if mips > 1 else 0), caps2, 0, 0, 0)
+    assert len(header) == 124
+    out = b"DDS " + header
+    if dxgi is not None:
+        out += struct.pack("<5I", dxgi, dimension, 0x4 if cube else 0, array, 0)
+    return out + bytes(payload)
+
+
+def dds_payload_bytes(width, height, depth, mips, elements, bits_per_pixel, block_bytes):
+    """Independent size computation (array element major, mips inside)."""
+    total = 0
+    for _ in range(elements):
+        w, h, d = width, height, max(depth, 1)
+        for _ in range(mips):
+            if block_bytes >= 8:
+                total += max(1, (w + 3) // 4) * max(1, (h + 3) // 4) * block_bytes * d
+            elif block_bytes == 4:
+                total += ((w + 1) // 2) * 4 * h * d
+            else:
+                total += ((w * bits_per_pixel + 7) // 8) * h * d
+            w, h, d = max(w // 2, 1), max(h // 2, 1), max(d // 2, 1)
+    return total

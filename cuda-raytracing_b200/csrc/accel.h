@@ -27,6 +27,9 @@
 #define RT_MAX_LEAF_PRIMS 16u
 // TriRecord::ref_leaf bit 31: the NEXT slot of the same leaf holds this face's duplicate (same v0, e1/e2 exchanged - the flat copy
 // Scene::AddLoadedScene appends to every smooth face, Scene.cpp:110-127); traverse.cuh skips it after a proven-margin miss.
+#ifndef RT_TW_TWIN
+#define RT_TW_TWIN 0   /* build switch shared by accel_build.cpp (pair + flag the copies) and traverse.cuh (skip them): measured slower, off */
+#endif
 #define RT_TWIN_BIT 0x80000000u
 #define RT_REF_LEAF_MASK 0x7FFFFFFFu
 #define RT_STACK_SIZE 64

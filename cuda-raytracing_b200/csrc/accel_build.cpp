@@ -210,7 +210,7 @@ int BuildAccelHost(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* 
     }
     if (invalid) return RT_E_INVALID;
     lap("gather records");
-    Builder builder{ nodes, node_count, fat_leaf_threshold, out, {}, {}, 0, std::getenv("B200RT_NO_TWINS") == nullptr };
+    Builder builder{ nodes, node_count, fat_leaf_threshold, out, {}, {}, 0, RT_TW_TWIN != 0 && std::getenv("B200RT_NO_TWINS") == nullptr };
     out.wide.reserve(node_count / 2 + 16);
     out.root_ref = builder.Emit(0, 0);
     lap("wide nodes");

@@ -267,9 +267,8 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
 #ifndef RT_TW_LEAN
 #define RT_TW_LEAN 0   /* mode 7, deferred: keep only (t, slot, key) of the best candidate in the loop; id, u, v are recomputed from the winner's record after it */
 #endif
-#ifndef RT_TW_TWIN
-#define RT_TW_TWIN 0   /* mode 7: skip the duplicate of a mesh face when the first copy misses by a proven margin (tri_test): bit-identical, measured slower (57.9 vs 56.3 ms), off */
-#endif
+// RT_TW_TWIN (accel.h), mode 7: skip the duplicate of a mesh face when the first copy misses by a proven margin (tri_test): bit-identical,
+// measured slower (57.9 vs 56.3 ms), off
 
 //   kDeferred (template): the exact reference-leaf box re-check (6 IEEE divisions, ~110 instructions, executed by the ~2 lanes
 //     that just accepted a candidate: 12 % of the megakernel's issue slots) is not done per accepted candidate but ONCE, on the

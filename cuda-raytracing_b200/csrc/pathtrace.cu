@@ -19,6 +19,9 @@
 #ifndef RT_PT_BINNING
 #define RT_PT_BINNING 0  // 1: measurement build of the cost-binned pixel -> lane experiment (slower the more global the binning: off)
 #endif
+#ifndef RT_PT_CARRY
+#define RT_PT_CARRY 0  // > 0: stragglers of a traversal round (at most this many lanes left) suspend and finish their ray in the next round (TraceCarry)
+#endif
 #ifndef RT_PT_FMA
 #define RT_PT_FMA 0  // 1: slab test of the path tracer in FMA form (traverse.cuh, kFma): 1 % faster on the bunny, 1.9x slower on config 4b
 #endif
@@ -109,6 +112,12 @@ __global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK))
         PathState ps;
         int sample = 0, bounce = 0;
         bool fresh = true;
+#if RT_PT_CARRY
+        uint32_t carry_stack[RT_STACK_SIZE];
+        TraceCarry carry; carry.stack = carry_stack; carry.node = RT_SENTINEL; carry.sp = 0; carry.resume = false; carry.threshold = RT_PT_CARRY;
+        float carry_start = 0.0f;
+        HitRecord h;
+#endif
         while (kLockstep ? __any_sync(lane_mask, sample < P.spp) : (sample < P.spp))
         {
             if (kLockstep)
@@ -131,9 +140,19 @@ __global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK))
                 r.t = 1e30f; r.id = RT_MISS_ID; r.slot = 0; r.key = RT_MISS_ID; r.bu = 0; r.bv = 0;
                 sphere_tests(S.spheres, S.sphere_count, ps.o, nd, r);
             };
+#if RT_PT_CARRY
+            if (kMode == 0)
+            {
+                if (!carry.resume) reinit(h);
+                if (!trace_wide_resumable<false, RT_PT_FMA != 0>(A, ps.o, ps.d, nd, h, reinit, carry, carry_start)) { carry.resume = true; continue; }
+                carry.resume = false;
+            }
+            else { reinit(h); trace_reference_order<false>(A, ps.o, ps.d, nd, h, &work_nodes, &work_tris); }
+#else
             HitRecord h; reinit(h);
             if (kMode == 0) trace_wide<false, RT_PT_FMA != 0>(A, ps.o, ps.d, nd, h, reinit, kCount ? &steps : nullptr);
             else trace_reference_order<false>(A, ps.o, ps.d, nd, h, &work_nodes, &work_tris);
+#endif
             rays++;
             bool alive;
             if (h.id != RT_MISS_ID) alive = shade_hit(A, S, h, ps, rng) && (++bounce < P.max_bounces);

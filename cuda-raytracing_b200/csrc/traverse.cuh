@@ -264,6 +264,9 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
 #ifndef RT_TW_MODE
 #define RT_TW_MODE 7
 #endif
+#ifndef RT_TW_CARRY_PERIOD
+#define RT_TW_CARRY_PERIOD 1
+#endif
 #ifndef RT_TW_LEAN
 #define RT_TW_LEAN 0   /* mode 7, deferred: keep only (t, slot, key) of the best candidate in the loop; id, u, v are recomputed from the winner's record after it */
 #endif
@@ -275,10 +278,25 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
 //     winner, after the loop. Unverified candidates only ever shrink the search interval, so any candidate that beats them is
 //     still found; if the WINNER's leaf box fails (a ray grazing a leaf box within rounding - rare) the function returns false
 //     and the caller redoes the ray with the per-candidate check (trace_wide below). Exact by construction.
-template <bool kTieById, bool kFma, bool kDeferred>
-__device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3 d, Vec3 nd, HitRecord& h, uint32_t* steps = nullptr)
+// Suspend / resume of one ray's traversal (mode 7): when only `threshold` lanes of the warp are still inside the loop (and more
+// than that entered it together), the stragglers leave with their state (current node reference, stack depth; the stack itself
+// lives in the caller's array, the best hit so far in `h`) and finish the ray in the caller's NEXT round, side by side with the
+// other lanes' new rays, instead of running the tail of this round alone. Per lane nothing changes: same steps, same order.
+struct TraceCarry
 {
-    const float start_length = h.t;
+    uint32_t* stack;     // caller-owned, RT_STACK_SIZE entries, untouched by the caller between suspend and resume
+    uint32_t node;
+    int sp;
+    bool resume;         // in: continue the suspended ray (h, node, sp, stack as left)
+    int threshold;       // suspend when at most this many lanes are left
+};
+enum : int { RT_TRACE_REDO = 0, RT_TRACE_DONE = 1, RT_TRACE_SUSPENDED = 2 };
+
+template <bool kTieById, bool kFma, bool kDeferred>
+__device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 d, Vec3 nd, HitRecord& h, uint32_t* steps = nullptr,
+                                               TraceCarry* carry = nullptr, float carry_start_length = 0.0f)
+{
+    const float start_length = (carry && carry->resume) ? carry_start_length : h.t;
     // reciprocal of the normalised direction; zero components -> huge finite (conservative)
     const float big = 1e30f;
     const float ix = nd.x != 0.0f ? 1.0f / nd.x : big, iy = nd.y != 0.0f ? 1.0f / nd.y : big, iz = nd.z != 0.0f ? 1.0f / nd.z : big;
@@ -288,7 +306,8 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
     const float cx = -ax, cy = -ay, cz = -az;
     const float slack = kFma ? 4.0e-7f * fmaxf(fabsf(ax), fmaxf(fabsf(ay), fabsf(az))) + 1e-30f : 0.0f;
 #define RT_SLAB(p, inv, c, oc) (kFma ? fmaf(p, inv, c) : (((p) - (oc)) * (inv)))
-    uint32_t stack[RT_STACK_SIZE];
+    uint32_t local_stack[RT_STACK_SIZE];
+    uint32_t* const stack = carry ? carry->stack : local_stack;
     int sp = 0;
 #if !RT_TW_SHSTACK
     stack[sp++] = RT_SENTINEL;
@@ -312,6 +331,10 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
     RT_PUSH(RT_SENTINEL);
 #endif
     uint32_t node = A.root_ref;
+    if (carry && carry->resume) { node = carry->node; sp = carry->sp; }  // (stack[0] is the sentinel either way)
+    // suspend limit of this round: -1 (never) unless more lanes entered together than the threshold - a round that starts with
+    // few lanes runs to completion, so every round finishes at least one ray
+    const int carry_limit = (carry && __popc(__activemask()) > carry->threshold) ? carry->threshold : -1;
 #if RT_TW_CACHE
     uint32_t verified = RT_SENTINEL;
     uint32_t* const verified_ptr = &verified;
@@ -497,6 +520,18 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
 #endif
     while (node != RT_SENTINEL)
     {
+        if (carry && __popc(__activemask()) <= carry_limit)
+        {
+            carry->node = node; carry->sp = sp;
+            return RT_TRACE_SUSPENDED;
+        }
+#if RT_TW_CARRY_PERIOD > 1
+      // the suspend vote costs ~7 instructions: take it once per RT_TW_CARRY_PERIOD steps (unrolled copies of the step)
+#pragma unroll
+      for (int carry_u = 0; carry_u < (carry ? RT_TW_CARRY_PERIOD : 1); carry_u++)
+      {
+        if (carry_u && node == RT_SENTINEL) break;
+#endif
         if (steps) (*steps)++;  // per-lane work measure (node + triangle steps) for cost-binned pixel scheduling
         const bool is_leaf = (node & RT_LEAF_BIT) != 0u;
         const uint32_t slot = node & 0x07FFFFFFu;
@@ -548,6 +583,9 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
             if (node & 0x78000000u) node = node - (1u << 27) + 1u;
             else RT_POP();
         }
+#if RT_TW_CARRY_PERIOD > 1
+      }
+#endif
     }
 #if RT_TW_LEAN
     if (kDeferred && win_slot != RT_SENTINEL)
@@ -663,11 +701,11 @@ __device__ __forceinline__ bool trace_wide_impl(const AccelView& A, Vec3 o, Vec3
     {   // h entered as a sphere hit or a miss, so a triangle id means "found here": verify its reference leaf (main_raytracing.cu:46)
         const uint32_t leaf = __ldg(&A.tris[h.slot].ref_leaf) & RT_REF_LEAF_MASK;
 #ifdef RT_TW_FORCE_REDO
-        if ((h.slot & RT_TW_FORCE_REDO) == 0u) return false;  // test hook: exercise the redo path on a fraction of the rays
+        if ((h.slot & RT_TW_FORCE_REDO) == 0u) return RT_TRACE_REDO;  // test hook: exercise the redo path on a fraction of the rays
 #endif
-        return exact_box(o, d, A.ref_nodes + leaf, start_length);
+        return exact_box(o, d, A.ref_nodes + leaf, start_length) ? RT_TRACE_DONE : RT_TRACE_REDO;
     }
-    return true;
+    return RT_TRACE_DONE;
 }
 
 template <bool kTieById, bool kFma>
@@ -681,12 +719,25 @@ template <bool kTieById, bool kFma = false, class Reinit>
 __device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, Vec3 nd, HitRecord& h, Reinit reinit, uint32_t* steps = nullptr)
 {
 #if RT_TW_DEFER
-    if (trace_wide_impl<kTieById, kFma, true>(A, o, d, nd, h, steps)) return;
+    if (trace_wide_impl<kTieById, kFma, true>(A, o, d, nd, h, steps) != RT_TRACE_REDO) return;
     reinit(h);
     trace_wide_checked<kTieById, kFma>(A, o, d, nd, h);
 #else
     trace_wide_impl<kTieById, kFma, false>(A, o, d, nd, h);
 #endif
+}
+
+// trace_wide with suspend / resume (TraceCarry). Returns false when the ray was suspended: the caller keeps `h`, `carry` and
+// `start_length` untouched and calls again with carry.resume = true (and the same o, d, nd). Deferred leaf-box check as above.
+template <bool kTieById, bool kFma = false, class Reinit>
+__device__ __forceinline__ bool trace_wide_resumable(const AccelView& A, Vec3 o, Vec3 d, Vec3 nd, HitRecord& h, Reinit reinit,
+                                                     TraceCarry& carry, float& start_length)
+{
+    if (!carry.resume) start_length = h.t;
+    const int r = trace_wide_impl<kTieById, kFma, true>(A, o, d, nd, h, nullptr, &carry, start_length);
+    if (r == RT_TRACE_SUSPENDED) return false;
+    if (r == RT_TRACE_REDO) { reinit(h); trace_wide_checked<kTieById, kFma>(A, o, d, nd, h); }
+    return true;
 }
 
 // Reference-order traversal over the reference-layout nodes: right child first, exact box test at

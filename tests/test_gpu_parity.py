@@ -265,6 +265,31 @@ def test_reference_named_entry_and_accumulation_semantics(rt, torch_cuda):
     assert np.allclose(got[..., :3] / 5, est.cpu().numpy()[..., :3], rtol=1e-6, atol=1e-7)
 
 
+def test_cost_ordered_tile_schedule_does_not_change_the_frame(rt, torch_cuda):
+    """With a workspace the megakernel schedules tiles heaviest-first from the previous launch's measured costs (pathtrace.cu).
+    Pixels are independent: three progressive frames with and without it are bit-identical in both surfaces and in every pixel's
+    RNG state; the order the third launch used is a permutation of the tiles, and a frame-size change resets the history."""
+    import ctypes as C
+    W, H = 200, 120
+    a = gpu_util.DeviceScene(rt, torch_cuda, W, H, "poseB", seed=77, env=True)
+    b = gpu_util.DeviceScene(rt, torch_cuda, W, H, "poseB", seed=77, env=True)
+    for k in range(3):
+        a.process(k, spp=4, bounces=4, write_last=1, ordered=True)
+        b.process(k, spp=4, bounces=4, write_last=1, ordered=False)
+    torch_cuda.cuda.synchronize()
+    assert torch_cuda.equal(a.surface, b.surface) and torch_cuda.equal(a.last, b.last) and torch_cuda.equal(a.rng, b.rng)
+    assert a.rays() == b.rays()
+    ws = a.workspace.view(torch_cuda.int32).cpu().numpy().view(np.uint32)
+    n = ((W + 15) // 16) * ((H + 7) // 8)
+    assert tuple(ws[:3]) == (W, H, n) and ws[3] == 2  # two launches found a cost history
+    order, cost = ws[4:4 + n], ws[4 + n:4 + 2 * n]
+    assert np.array_equal(np.sort(order), np.arange(n, dtype=np.uint32))
+    assert (cost > 0).all()  # every tile ran and reported
+    prev = b.workspace  # the other scene's workspace was never used
+    assert int(prev.view(torch_cuda.int32).abs().sum().item()) == 0
+    assert rt.lib().rt_process_workspace_bytes(W, H, 0) == (4 + 2 * max(n, (W * H + 127) // 128)) * 4
+
+
 def test_sample_split_is_stream_continuous(rt, torch_cuda):
     """One launch of 10 spp == two launches of 5 spp (sum buffers): the per-pixel stream is continuous across launches."""
     t = torch_cuda

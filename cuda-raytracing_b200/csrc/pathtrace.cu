@@ -19,6 +19,9 @@
 #ifndef RT_PT_BINNING
 #define RT_PT_BINNING 0  // 1: measurement build of the cost-binned pixel -> lane experiment (slower the more global the binning: off)
 #endif
+#ifndef RT_PT_WARP_W
+#define RT_PT_WARP_W 8
+#endif
 #ifndef RT_PT_CARRY
 #define RT_PT_CARRY 0  // > 0: stragglers of a traversal round (at most this many lanes left) suspend and finish their ray in the next round (TraceCarry)
 #endif
@@ -91,8 +94,10 @@ __global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK))
         bx = tile % tiles_x; by = tile / tiles_x;
         t_start = clock64();
     }
-    int x = bx * 16 + (warp & 1) * 8 + (lane & 7);
-    int y = by * (RT_PT_BLOCK / 16) + (warp >> 1) * 4 + (lane >> 3);
+    // warp footprint inside the 16-wide CTA tile: RT_PT_WARP_W x (32 / RT_PT_WARP_W) pixels (8 x 4 measured best: 4 x 8 .., 16 x 2 ..)
+    constexpr int kWarpsX = 16 / RT_PT_WARP_W, kWarpH = 32 / RT_PT_WARP_W;
+    int x = bx * 16 + (warp % kWarpsX) * RT_PT_WARP_W + (lane % RT_PT_WARP_W);
+    int y = by * (RT_PT_BLOCK / 16) + (warp / kWarpsX) * kWarpH + (lane / RT_PT_WARP_W);
     bool active = x < P.width && y < P.height;
     if (RT_PT_BINNING && P.pixel_perm)
     {

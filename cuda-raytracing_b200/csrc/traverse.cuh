@@ -13,6 +13,10 @@
 #include <cstdint>
 #include "accel.h"
 
+#ifndef RT_TW_TRI_STAGED
+#define RT_TW_TRI_STAGED 0   /* tri_test: u range test before the second triple product is evaluated: one more divergent branch, 54.9 vs 52.9 ms, off */
+#endif
+
 struct Vec3 { float x, y, z; };
 
 __device__ __forceinline__ Vec3 mk3(float x, float y, float z) { Vec3 v; v.x = x; v.y = y; v.z = z; return v; }
@@ -91,10 +95,20 @@ __device__ __forceinline__ bool tri_test(Vec3 o, Vec3 nd, float4 r0, float4 r1, 
     {
         const Vec3 dist = o - v0;
         const float u = dot3(dist, p);
-        const Vec3 perp = cross3(dist, e1);
-        const float v = dot3(nd, perp);
         const bool want_twin = twin_clear_miss && *twin_clear_miss;  // in: this record's copy sits in the next slot
         if (twin_clear_miss) *twin_clear_miss = false;               // out: the copy provably misses as well
+#if RT_TW_TRI_STAGED
+        // the u range test first, cross(dist, e1) and v only for the lanes that pass it (same operations, same roundings: GLM's own
+        // order of the TESTS, intersect.inl:55-63; without this the compiler evaluates both triple products before the first branch)
+        if (!want_twin)
+        {
+            if (det > FLT_EPSILON) { if (u < 0.0f || u > det) return false; }
+            else if (det < -FLT_EPSILON) { if (u > 0.0f || u < det) return false; }
+            else return false;
+        }
+#endif
+        const Vec3 perp = cross3(dist, e1);
+        const float v = dot3(nd, perp);
         bool miss;
         if (det > FLT_EPSILON) miss = (u < 0.0f || u > det) || (v < 0.0f || (u + v) > det);
         else if (det < -FLT_EPSILON) miss = (u > 0.0f || u < det) || (v > 0.0f || (u + v) < det);

@@ -13,6 +13,9 @@
 #include <cstdint>
 #include "accel.h"
 
+#ifndef RT_TW_TRI_PACKED
+#define RT_TW_TRI_PACKED 1   /* tri_test in packed fp32 (FMUL2 / FADD2), bit-identical: 52.9 -> 51.3 ms */
+#endif
 #ifndef RT_TW_TRI_STAGED
 #define RT_TW_TRI_STAGED 0   /* tri_test: u range test before the second triple product is evaluated: one more divergent branch, 54.9 vs 52.9 ms, off */
 #endif
@@ -88,6 +91,92 @@ template <bool kNegO = false>
 __device__ __forceinline__ bool tri_test(Vec3 o, Vec3 nd, float4 r0, float4 r1, float4 r2, float& t, float& bu, float& bv,
                                          bool* twin_clear_miss = nullptr)
 {
+#if RT_TW_TRI_PACKED
+    if (kNegO && !twin_clear_miss)
+    {   // packed form on the NEGATED origin (the slab test's own -o pair): every intermediate that involves dist is the exact negation
+        // of GLM's (round-to-nearest is sign-symmetric), the range tests are mirrored, and the division by -det hands back GLM's t, u, v
+        const float2 e1xy = make_float2(r1.x, r1.y), e2xy = make_float2(r2.x, r2.y);
+        const float2 nd_xy = make_float2(nd.x, nd.y), nd_yx = make_float2(nd.y, nd.x);
+        const float2 pa = __fmul2_rn(e2xy, make_float2(nd.z, nd.z));
+        const float2 pb = __fmul2_rn(e2xy, nd_yx);
+        const float2 pc = __fmul2_rn(nd_yx, make_float2(r2.z, r2.z));
+        const float2 pxy = make_float2(pc.x - pa.y, pa.x - pc.y);
+        const float pz = pb.y - pb.x;
+        const float2 dd = __fmul2_rn(e1xy, pxy);
+        const float det = (dd.x + dd.y) + r1.z * pz;
+        const float2 dxy = __fadd2_rn(make_float2(o.x, o.y), make_float2(r0.x, r0.y));  // (-origin) + v0 = -(origin - v0)
+        const float dz = o.z + r0.z;
+        const float2 uu = __fmul2_rn(dxy, pxy);
+        const float un = (uu.x + uu.y) + dz * pz;                                        // -u
+        const float2 d_yx = make_float2(dxy.y, dxy.x);
+        const float2 qa = __fmul2_rn(e1xy, make_float2(dz, dz));
+        const float2 qb = __fmul2_rn(e1xy, d_yx);
+        const float2 qc = __fmul2_rn(d_yx, make_float2(r1.z, r1.z));
+        const float2 qxy = make_float2(qc.x - qa.y, qa.x - qc.y);                         // -cross(dist, e1).xy
+        const float qz = qb.y - qb.x;
+        const float2 vv = __fmul2_rn(nd_xy, qxy);
+        const float vn = (vv.x + vv.y) + nd.z * qz;                                       // -v
+        const float ndet = -det;
+        if (det > FLT_EPSILON)
+        {
+            if (un > 0.0f || un < ndet) return false;
+            if (vn > 0.0f || (un + vn) < ndet) return false;
+        }
+        else if (det < -FLT_EPSILON)
+        {
+            if (un < 0.0f || un > ndet) return false;
+            if (vn < 0.0f || (un + vn) > ndet) return false;
+        }
+        else return false;
+        const float ninv = 1.0f / ndet;                                                   // = -(1 / det) exactly
+        const float2 tt = __fmul2_rn(e2xy, qxy);
+        t = ((tt.x + tt.y) + r2.z * qz) * ninv;
+        bu = un * ninv; bv = vn * ninv;
+        return true;
+    }
+    if (!kNegO && !twin_clear_miss)
+    {   // the same products and sums, two multiplies / adds per instruction where operands pair up (Blackwell FMUL2 / FADD2, IEEE
+        // round-to-nearest per lane): every product below is one of GLM's with its factors possibly exchanged (exact), every sum has
+        // GLM's operands in GLM's order. Pairs: (x, y) of v0 / e1 / e2 straight from the 128-bit loads, (x, y) and (y, x) of the ray.
+        const float2 e1xy = make_float2(r1.x, r1.y), e2xy = make_float2(r2.x, r2.y);
+        const float2 nd_xy = make_float2(nd.x, nd.y), nd_yx = make_float2(nd.y, nd.x);
+        const float2 pa = __fmul2_rn(e2xy, make_float2(nd.z, nd.z));   // e2.x nd.z | e2.y nd.z
+        const float2 pb = __fmul2_rn(e2xy, nd_yx);                     // e2.x nd.y | e2.y nd.x
+        const float2 pc = __fmul2_rn(nd_yx, make_float2(r2.z, r2.z));  // nd.y e2.z | nd.x e2.z
+        const float2 pxy = make_float2(pc.x - pa.y, pa.x - pc.y);      // cross(nd, e2).xy
+        const float pz = pb.y - pb.x;
+        const float2 dd = __fmul2_rn(e1xy, pxy);
+        const float det = (dd.x + dd.y) + r1.z * pz;
+        const float2 dxy = __fadd2_rn(make_float2(o.x, o.y), make_float2(-r0.x, -r0.y));  // o - v0
+        const float dz = o.z - r0.z;
+        const float2 uu = __fmul2_rn(dxy, pxy);
+        const float u = (uu.x + uu.y) + dz * pz;
+        const float2 d_yx = make_float2(dxy.y, dxy.x);
+        const float2 qa = __fmul2_rn(e1xy, make_float2(dz, dz));       // e1.x d.z | e1.y d.z
+        const float2 qb = __fmul2_rn(e1xy, d_yx);                      // e1.x d.y | e1.y d.x
+        const float2 qc = __fmul2_rn(d_yx, make_float2(r1.z, r1.z));   // d.y e1.z | d.x e1.z
+        const float2 qxy = make_float2(qc.x - qa.y, qa.x - qc.y);      // cross(dist, e1).xy
+        const float qz = qb.y - qb.x;
+        const float2 vv = __fmul2_rn(nd_xy, qxy);
+        const float v = (vv.x + vv.y) + nd.z * qz;
+        if (det > FLT_EPSILON)
+        {
+            if (u < 0.0f || u > det) return false;
+            if (v < 0.0f || (u + v) > det) return false;
+        }
+        else if (det < -FLT_EPSILON)
+        {
+            if (u > 0.0f || u < det) return false;
+            if (v > 0.0f || (u + v) < det) return false;
+        }
+        else return false;
+        const float inv_det = 1.0f / det;
+        const float2 tt = __fmul2_rn(e2xy, qxy);
+        t = ((tt.x + tt.y) + r2.z * qz) * inv_det;
+        bu = u * inv_det; bv = v * inv_det;
+        return true;
+    }
+#endif
     const Vec3 v0 = mk3(r0.x, r0.y, r0.z), e1 = mk3(r1.x, r1.y, r1.z), e2 = mk3(r2.x, r2.y, r2.z);
     const Vec3 p = cross3(nd, e2);
     const float det = dot3(e1, p);

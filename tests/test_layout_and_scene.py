@@ -28,6 +28,23 @@ def test_library_exports_every_declared_symbol(rt):
     assert declared <= set(rt.SYMBOLS), declared - set(rt.SYMBOLS)
 
 
+def test_shipped_sass_has_no_contracted_packed_fma(rt):
+    """Contraction policy guard: the device code is built with -fmad=false so that every a*b+c rounds
+    twice like the host-compiled reference. nvcc nevertheless fuses a packed __fmul2_rn feeding a packed __fadd2_rn into FFMA2; the
+    product's packed code is written so that this never happens (the FMA slab form, RT_PT_FMA, is off). Scalar FFMA may only appear
+    where fmaf() is written (conservative box culls) and inside the IEEE division / sqrt sequences."""
+    import shutil
+    import subprocess
+    from _loader import load_build
+    tool = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(tool):
+        import pytest
+        pytest.skip("cuobjdump not available")
+    sass = subprocess.run([tool, "-sass", load_build().LIB], capture_output=True, text=True).stdout
+    assert "pathtrace_megakernel" in sass and "FMUL2" in sass and "FADD2" in sass  # the packed paths are really there
+    assert "FFMA2" not in sass
+
+
 def test_pod_layout_matches_reference_structs(rt, ref):
     s = ref.lib().ref_sizeof
     assert [s(i) for i in range(8)] == [32, 16, 32, 64, 32, 60, 136, 48]

@@ -14,7 +14,7 @@ struct PathConsts
 };
 
 __device__ __forceinline__ float mix1(float x, float y, float a) { return x * (1.0f - a) + y * a; }
-__device__ __forceinline__ Vec3 mix3(Vec3 x, Vec3 y, float a) { return mk3(mix1(x.x, y.x, a), mix1(x.y, y.y, a), mix1(x.z, y.z, a)); }
+__device__ __forceinline__ Vec3 mix3(Vec3 x, Vec3 y, float a) { return x * (1.0f - a) + y * a; }  // per component mix1: x*(1-a) + y*a (packed multiplies)
 __device__ __forceinline__ float glm_max(float a, float b) { return (a < b) ? b : a; }
 __device__ __forceinline__ float glm_min(float a, float b) { return (b < a) ? b : a; }
 

@@ -13,6 +13,9 @@
 #include <cstdint>
 #include "accel.h"
 
+#ifndef RT_VEC3_PACKED_MUL
+#define RT_VEC3_PACKED_MUL 1   /* vec3 multiplies as FMUL2 (adds stay scalar), bit-identical: 51.3 -> 50.8 ms */
+#endif
 #ifndef RT_TW_TRI_PACKED
 #define RT_TW_TRI_PACKED 1   /* tri_test in packed fp32 (FMUL2 / FADD2), bit-identical: 52.9 -> 51.3 ms */
 #endif
@@ -26,6 +29,27 @@ __device__ __forceinline__ Vec3 mk3(float x, float y, float z) { Vec3 v; v.x = x
 __device__ __forceinline__ Vec3 operator+(Vec3 a, Vec3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
 __device__ __forceinline__ Vec3 operator-(Vec3 a, Vec3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
 __device__ __forceinline__ Vec3 operator-(Vec3 a) { return mk3(-a.x, -a.y, -a.z); }
+#if RT_VEC3_PACKED_MUL
+// The MULTIPLIES of the vec3 algebra two at a time (Blackwell FMUL2 on the x and y lanes; IEEE round-to-nearest per lane, factors
+// exchanged at most - exact), every ADD scalar and in GLM's order. Adds are deliberately NOT packed: ptxas fuses a packed multiply
+// that feeds a packed add into FFMA2 even under -fmad=false (one rounding instead of two; tests/test_layout_and_scene.py guards
+// the shipped SASS against any FFMA2).
+__device__ __forceinline__ float2 xy_(Vec3 a) { return make_float2(a.x, a.y); }
+__device__ __forceinline__ Vec3 operator*(Vec3 a, Vec3 b) { const float2 m = __fmul2_rn(xy_(a), xy_(b)); return mk3(m.x, m.y, a.z * b.z); }
+__device__ __forceinline__ Vec3 operator*(Vec3 a, float s) { const float2 m = __fmul2_rn(xy_(a), make_float2(s, s)); return mk3(m.x, m.y, a.z * s); }
+__device__ __forceinline__ Vec3 operator*(float s, Vec3 a) { const float2 m = __fmul2_rn(make_float2(s, s), xy_(a)); return mk3(m.x, m.y, s * a.z); }
+__device__ __forceinline__ Vec3 operator/(Vec3 a, float s) { return mk3(a.x / s, a.y / s, a.z / s); }
+// glm/detail/func_geometric.inl:48-54,68-78,82-89 ; func_exponential.inl:136-139
+__device__ __forceinline__ float dot3(Vec3 a, Vec3 b) { const float2 m = __fmul2_rn(xy_(a), xy_(b)); return m.x + m.y + a.z * b.z; }
+__device__ __forceinline__ Vec3 cross3(Vec3 x, Vec3 y)
+{
+    const float2 x_yx = make_float2(x.y, x.x);
+    const float2 a = __fmul2_rn(xy_(y), make_float2(x.z, x.z));  // y.x x.z | y.y x.z
+    const float2 b = __fmul2_rn(xy_(y), x_yx);                   // y.x x.y | y.y x.x
+    const float2 c = __fmul2_rn(x_yx, make_float2(y.z, y.z));    // x.y y.z | x.x y.z
+    return mk3(c.x - a.y, a.x - c.y, b.y - b.x);
+}
+#else
 __device__ __forceinline__ Vec3 operator*(Vec3 a, Vec3 b) { return mk3(a.x * b.x, a.y * b.y, a.z * b.z); }
 __device__ __forceinline__ Vec3 operator*(Vec3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
 __device__ __forceinline__ Vec3 operator*(float s, Vec3 a) { return mk3(s * a.x, s * a.y, s * a.z); }
@@ -33,6 +57,7 @@ __device__ __forceinline__ Vec3 operator/(Vec3 a, float s) { return mk3(a.x / s,
 // glm/detail/func_geometric.inl:48-54,68-78,82-89 ; func_exponential.inl:136-139
 __device__ __forceinline__ float dot3(Vec3 a, Vec3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 __device__ __forceinline__ Vec3 cross3(Vec3 x, Vec3 y) { return mk3(x.y * y.z - y.y * x.z, x.z * y.x - y.z * x.x, x.x * y.y - y.x * x.y); }
+#endif
 __device__ __forceinline__ Vec3 normalize3(Vec3 v) { return v * (1.0f / sqrtf(dot3(v, v))); }
 
 struct HitRecord

@@ -12,8 +12,13 @@
 //            with the face id and the owning reference leaf in the spare lanes;
 //   ShadeRecord (48 B) per slot: the three vertex normals and the material index, read once per hit.
 //
-// Child reference (u32): bit31 = 0 -> index of a WideNode; bit31 = 1 -> leaf:
-//   bits 27..30 = prim_count-1 (<= 16 prims), bits 0..26 = first slot. 0xFFFFFFFF = stack sentinel.
+// Child reference (u32). WideNodes and TriRecords live in ONE device arena (< 2 GiB) and a reference IS the byte offset of its
+// record, so the traversal loop forms the address of either kind with one mask and one add, no select and no scaling:
+//   bit31 = 0 -> WideNode at byte offset bits 4..30 (bits 0..3 zero);
+//   bit31 = 1 -> leaf: bits 4..30 = byte offset of its first TriRecord (records of a leaf are consecutive, 48 B each),
+//                bits 0..3 = prim_count-1 (<= 16 prims; the offset's own low four bits are zero: records are 16-B aligned).
+//   "Next triangle of this leaf" = ref + 48 - 1. 0xFFFFFFFF = stack sentinel.
+//   Slot (index into tris / shade) = (offset - tri_byte0) / 48. 2 GiB of nodes + triangles = ~27 M triangles.
 // Reference leaves with more than `fat_leaf_threshold` prims (BVH.cpp never bounds leaf size; the
 // bunny scene has one of 345) keep their exact box in the parent and get a private sub-tree of
 // WideNodes over their own slots with conservatively inflated boxes (leaf contents unchanged).
@@ -24,6 +29,8 @@
 
 #define RT_LEAF_BIT 0x80000000u
 #define RT_SENTINEL 0xFFFFFFFFu
+#define RT_REF_BYTE_MASK 0x7FFFFFF0u
+#define RT_REF_COUNT_MASK 0x0000000Fu
 #define RT_MAX_LEAF_PRIMS 16u
 // TriRecord::ref_leaf bit 31: the NEXT slot of the same leaf holds this face's duplicate (same v0, e1/e2 exchanged - the flat copy
 // Scene::AddLoadedScene appends to every smooth face, Scene.cpp:110-127); traverse.cuh skips it after a proven-margin miss.
@@ -68,6 +75,7 @@ struct AccelHost
     std::vector<TriRecord> tris;       // one per BVH slot
     std::vector<ShadeRecord> shade;    // one per BVH slot
     uint32_t root_ref = RT_SENTINEL;
+    uint32_t tri_byte0 = 0;            // byte offset of tris[0] in the arena = 64 * wide.size()
     uint32_t ref_leaf_count = 0, fat_leaf_count = 0, wide_depth = 0, ref_depth = 0, twin_pair_count = 0;
 };
 
@@ -79,12 +87,14 @@ int BuildAccelHost(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* 
 // Device-side view passed to kernels by value.
 struct AccelView
 {
-    const WideNode* wide;
-    const TriRecord* tris;
+    const char* arena;           // wide nodes, then triangle records (what references address, as byte offsets)
+    const WideNode* wide;        // = arena
+    const TriRecord* tris;       // = arena + tri_byte0
     const ShadeRecord* shade;
     const RtBVHNode* ref_nodes;  // device copy of the reference nodes (exact leaf boxes, reference-order kernel)
     uint32_t root_ref;
     uint32_t node_count;
+    uint32_t tri_byte0;
 };
 
 struct RtAccel

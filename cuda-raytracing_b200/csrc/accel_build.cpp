@@ -217,5 +217,18 @@ int BuildAccelHost(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* 
     if (builder.error) return builder.error;
     if (out.wide_depth + 2 > RT_STACK_SIZE || out.ref_depth + 2 > RT_STACK_SIZE) return RT_E_DEPTH;
     if (out.wide.empty()) out.wide.push_back(WideNode{});  // keep the device array non-empty
+    // internal (count-1) << 27 | index references -> byte offsets into the (wide nodes | triangle records) arena (accel.h)
+    const uint64_t tri_byte0 = (uint64_t)out.wide.size() * sizeof(WideNode);
+    if (tri_byte0 + (uint64_t)out.tris.size() * sizeof(TriRecord) + 64 > RT_REF_BYTE_MASK) return RT_E_INVALID;  // > 2 GiB of nodes + triangles
+    out.tri_byte0 = (uint32_t)tri_byte0;
+    auto to_offset = [&](uint32_t r) -> uint32_t
+    {
+        if (r == RT_SENTINEL) return r;
+        if (r & RT_LEAF_BIT) return RT_LEAF_BIT | (uint32_t)(tri_byte0 + (uint64_t)(r & 0x07FFFFFFu) * sizeof(TriRecord)) | ((r >> 27) & 0xFu);
+        return r * (uint32_t)sizeof(WideNode);
+    };
+    for (WideNode& w : out.wide) { w.child[0] = to_offset(w.child[0]); w.child[1] = to_offset(w.child[1]); }
+    out.root_ref = to_offset(out.root_ref);
+    lap("byte-offset refs");
     return 0;
 }

@@ -93,8 +93,9 @@ int rt_accel_create(const RtBVHNode* nodes, uint32_t node_count, const uint32_t*
     WideNode* d_wide = nullptr; TriRecord* d_tris = nullptr; ShadeRecord* d_shade = nullptr; RtBVHNode* d_ref = nullptr;
     const size_t bw = host.wide.size() * sizeof(WideNode), bt = host.tris.size() * sizeof(TriRecord);
     const size_t bs = host.shade.size() * sizeof(ShadeRecord), br = (size_t)node_count * sizeof(RtBVHNode);
-    cudaError_t e = cudaMalloc(&d_wide, bw);
-    if (e == cudaSuccess) e = cudaMalloc(&d_tris, bt + 64);  // + pad: the unified fetch of trace_wide reads 56 B from the last record
+    // one arena: wide nodes, then triangle records (references are 16-byte unit offsets into it, accel.h)
+    cudaError_t e = cudaMalloc(&d_wide, bw + bt + 64);  // + pad: the unified fetch of trace_wide reads 56 B from the last record
+    if (e == cudaSuccess) d_tris = reinterpret_cast<TriRecord*>(reinterpret_cast<char*>(d_wide) + bw);
     if (e == cudaSuccess) e = cudaMalloc(&d_shade, bs);
     if (e == cudaSuccess) e = cudaMalloc(&d_ref, br);
     if (e == cudaSuccess) e = cudaMemcpy(d_wide, host.wide.data(), bw, cudaMemcpyHostToDevice);
@@ -103,12 +104,12 @@ int rt_accel_create(const RtBVHNode* nodes, uint32_t node_count, const uint32_t*
     if (e == cudaSuccess) e = cudaMemcpy(d_ref, nodes, br, cudaMemcpyHostToDevice);
     if (e != cudaSuccess)
     {
-        cudaFree(d_wide); cudaFree(d_tris); cudaFree(d_shade); cudaFree(d_ref); delete a;
+        cudaFree(d_wide); cudaFree(d_shade); cudaFree(d_ref); delete a;
         return CudaFail(e, "rt_accel_create upload");
     }
     if (timing) fprintf(stderr, "[accel] %-20s %8.1f ms (%.0f MB)\n", "upload", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_upload).count(), (bw + bt + bs + br) / 1e6);
-    a->view.wide = d_wide; a->view.tris = d_tris; a->view.shade = d_shade; a->view.ref_nodes = d_ref;
-    a->view.root_ref = host.root_ref; a->view.node_count = node_count;
+    a->view.arena = reinterpret_cast<const char*>(d_wide); a->view.wide = d_wide; a->view.tris = d_tris; a->view.shade = d_shade; a->view.ref_nodes = d_ref;
+    a->view.root_ref = host.root_ref; a->view.node_count = node_count; a->view.tri_byte0 = host.tri_byte0;
     a->device_bytes = bw + bt + bs + br;
     a->wide_count = (uint32_t)host.wide.size(); a->slot_count = (uint32_t)host.tris.size();
     a->ref_leaf_count = host.ref_leaf_count; a->fat_leaf_count = host.fat_leaf_count;
@@ -124,7 +125,7 @@ int rt_accel_destroy(RtAccel* a)
         std::lock_guard<std::mutex> lock(g_mutex);
         for (auto it = g_bound.begin(); it != g_bound.end();) it = it->second == a ? g_bound.erase(it) : std::next(it);
     }
-    cudaFree((void*)a->view.wide); cudaFree((void*)a->view.tris); cudaFree((void*)a->view.shade); cudaFree((void*)a->view.ref_nodes);
+    cudaFree((void*)a->view.arena); cudaFree((void*)a->view.shade); cudaFree((void*)a->view.ref_nodes);
     delete a;
     return RT_OK;
 }

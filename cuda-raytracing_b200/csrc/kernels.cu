@@ -222,7 +222,7 @@ struct ExtendLane
 template <bool kTieById>
 __device__ __forceinline__ void extend_leaf(const AccelView& A, uint32_t leaf, ExtendLane& L)
 {
-    const uint32_t first = leaf & 0x07FFFFFFu, count = ((leaf >> 27) & 0xFu) + 1u;
+    const uint32_t first = ref_slot(A, leaf), count = ref_count(leaf);
     const TriRecord* tr = A.tris + first;
     for (uint32_t i = 0; i < count; i++)
     {
@@ -246,7 +246,7 @@ __device__ __forceinline__ void extend_leaf(const AccelView& A, uint32_t leaf, E
 __device__ __forceinline__ void extend_inner(const AccelView& A, ExtendLane& L, uint32_t* stack)
 {
     const float kWiden = 1.0e-6f;
-    const WideNode* w = A.wide + L.node;
+    const WideNode* w = ref_wide(A, L.node);
     const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32);
     const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
     float t1 = fmaf(a.x, L.ix, L.cx), t2 = fmaf(a.z, L.ix, L.cx);

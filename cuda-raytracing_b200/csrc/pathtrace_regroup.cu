@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(256, kMinBlocks) pathtrace_regroup_kernel(Acce
         const unsigned m_leaf = __ballot_sync(FULL, on_leaf), m_inner = __ballot_sync(FULL, trav && !on_leaf);
         if (trav && !on_leaf)
         {
-            const WideNode* w = A.wide + node;
+            const WideNode* w = ref_wide(A, node);
             const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32);
             const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
             // exact slab form (plane - o) * inv in packed fp32, three-compare conservative cull (traverse.cuh)
@@ -205,8 +205,8 @@ __global__ void __launch_bounds__(256, kMinBlocks) pathtrace_regroup_kernel(Acce
         }
         if (on_leaf && (__popc(m_leaf) >= P.leaf_batch || m_inner == 0u))
         {   // one triangle; the leaf reference is re-encoded with the remaining range. No per-candidate leaf-box check (deferred).
-            leaf_tests<false, false>(A, node & 0x07FFFFFFu, 1u, ps.o, ps.d, nd, start_length, h);
-            if (node & 0x78000000u) node = node - (1u << 27) + 1u;
+            leaf_tests<false, false>(A, ref_slot(A, node), 1u, ps.o, ps.d, nd, start_length, h);
+            if (ref_has_more(node)) node = ref_next_tri(node);
             else node = stack[--sp];
         }
         if (trav && node == RT_SENTINEL)

@@ -74,6 +74,16 @@ struct HitRecord
 
 __device__ __forceinline__ float4 ldg4(const void* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 
+// Node / leaf references are byte offsets into the accel arena (accel.h): one address form for both kinds of record.
+__device__ __forceinline__ const char* ref_record(const AccelView& A, uint32_t ref) { return A.arena + (ref & RT_REF_BYTE_MASK); }
+__device__ __forceinline__ const WideNode* ref_wide(const AccelView& A, uint32_t ref) { return reinterpret_cast<const WideNode*>(ref_record(A, ref)); }
+// byte offset -> slot: exact division by 48 = shift by 4, then multiplication by the inverse of 3 modulo 2^32 (the quotient is exact)
+__device__ __forceinline__ uint32_t offset_slot(const AccelView& A, uint32_t offset) { return ((offset - A.tri_byte0) >> 4) * 0xAAAAAAABu; }
+__device__ __forceinline__ uint32_t ref_slot(const AccelView& A, uint32_t ref) { return offset_slot(A, ref & RT_REF_BYTE_MASK); }
+__device__ __forceinline__ uint32_t ref_count(uint32_t ref) { return (ref & RT_REF_COUNT_MASK) + 1u; }
+__device__ __forceinline__ bool ref_has_more(uint32_t ref) { return (ref & RT_REF_COUNT_MASK) != 0u; }
+__device__ __forceinline__ uint32_t ref_next_tri(uint32_t ref, uint32_t step = 1u) { return ref + 47u * step; }  // +48 bytes, -1 prim each; caller checked the count
+
 // Math::IntersectAABB with the reference's operand roles. Order-independent use: ray_length = the
 // distance the BVH search STARTED with (sphere hit or 1e30).
 // kInclusive: `tmin <= ray_length` instead of the reference's `<` - used only by the lowest-id tie rule, where a node whose
@@ -503,7 +513,7 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
     const float cnx = cx - ex, cny = cy - ey, cnz = cz - ez, cfx = cx + ex, cfy = cy + ey, cfz = cz + ez;
 #define RT_NODE_STEP()                                                                                                     \
     do {                                                                                                                    \
-        const WideNode* w = A.wide + node;                                                                                  \
+        const WideNode* w = ref_wide(A, node);                                                                              \
         const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32); \
         const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));                      \
         RT_NODE_MATH(a, b, c, ch);                                                                                          \
@@ -512,8 +522,8 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
     do {                                                                                                                    \
         if (RT_TW_PREFETCH_CHILD)                                                                                           \
         {   /* experiment: start the L2->L1 fetch of both children's records while this node's boxes are tested */        \
-            const char* c0 = (ch.x & RT_LEAF_BIT) ? reinterpret_cast<const char*>(A.tris + (ch.x & 0x07FFFFFFu)) : reinterpret_cast<const char*>(A.wide + ch.x); \
-            const char* c1 = (ch.y & RT_LEAF_BIT) ? reinterpret_cast<const char*>(A.tris + (ch.y & 0x07FFFFFFu)) : reinterpret_cast<const char*>(A.wide + ch.y); \
+            const char* c0 = ref_record(A, ch.x); \
+            const char* c1 = ref_record(A, ch.y); \
             asm volatile("prefetch.global.L1 [%0];" ::"l"(c0));                                                             \
             asm volatile("prefetch.global.L1 [%0];" ::"l"(c1));                                                             \
         }                                                                                                                   \
@@ -600,7 +610,7 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
         else if (hit1) node = ch.y;                                                                                         \
         else RT_POP();                                                                                                      \
     } while (0)
-#define RT_LEAF_STEP(ref) leaf_tests<!kDeferred, kTieById>(A, (ref) & 0x07FFFFFFu, (((ref) >> 27) & 0xFu) + 1u, o, d, nd, start_length, h, verified_ptr)
+#define RT_LEAF_STEP(ref) leaf_tests<!kDeferred, kTieById>(A, ref_slot(A, (ref)), ref_count(ref), o, d, nd, start_length, h, verified_ptr)
 
 #if RT_TW_PARK && RT_TW_MODE == 7
     __shared__ uint32_t park_store[5 * 256];  // blocks of this library's traversal kernels have at most 256 threads
@@ -628,8 +638,8 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
         if (!(node & RT_LEAF_BIT)) RT_NODE_STEP();
         else
         {
-            leaf_tests<!kDeferred, kTieById>(A, node & 0x07FFFFFFu, 1u, o, d, nd, start_length, h, verified_ptr);
-            if (node & 0x78000000u) node = node - (1u << 27) + 1u;
+            leaf_tests<!kDeferred, kTieById>(A, ref_slot(A, node), 1u, o, d, nd, start_length, h, verified_ptr);
+            if (ref_has_more(node)) node = ref_next_tri(node);
             else RT_POP();
         }
     }
@@ -647,8 +657,8 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
             if (inner) RT_NODE_STEP();
             if (leaf && (__popc(m_leaf) >= RT_TW_BATCH || m_inner == 0u))
             {
-                leaf_tests<!kDeferred, kTieById>(A, node & 0x07FFFFFFu, 1u, o, d, nd, start_length, h, verified_ptr);
-                if (node & 0x78000000u) node = node - (1u << 27) + 1u;
+                leaf_tests<!kDeferred, kTieById>(A, ref_slot(A, node), 1u, o, d, nd, start_length, h, verified_ptr);
+                if (ref_has_more(node)) node = ref_next_tri(node);
                 else RT_POP();
             }
         }
@@ -679,12 +689,12 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
 #endif
         if (steps) (*steps)++;  // per-lane work measure (node + triangle steps) for cost-binned pixel scheduling
         const bool is_leaf = (node & RT_LEAF_BIT) != 0u;
-        const uint32_t slot = node & 0x07FFFFFFu;
-        const char* rec = is_leaf ? reinterpret_cast<const char*>(A.tris + slot) : reinterpret_cast<const char*>(A.wide + node);
+        const uint32_t slot = node & RT_REF_BYTE_MASK;  // arena byte offset; a winner's h.slot is converted to its slot after the loop
+        const char* rec = A.arena + slot;                // one address form for wide nodes and triangle records
         const float4 q0 = ldg4(rec), q1 = ldg4(rec + 16), q2 = ldg4(rec + 32);
         const uint2 q3 = __ldg(reinterpret_cast<const uint2*>(rec + 48));
 #if RT_TW_PREFETCH
-        if (is_leaf && (node & 0x78000000u))
+        if (is_leaf && ref_has_more(node))
         {   // the next record of this leaf is the next iteration's fetch: start it now (matters when the scene is not L2-resident)
             asm volatile("prefetch.global.L1 [%0];" ::"l"(rec + 64));
             asm volatile("prefetch.global.L1 [%0];" ::"l"(rec + 95));
@@ -703,7 +713,7 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
                     const uint32_t key = kTieById ? __float_as_uint(q0.w) : __float_as_uint(q2.w);
                     if (t < h.t || (win_slot != RT_SENTINEL && key < win_key)) { h.t = t; win_slot = slot; win_key = key; }
                 }
-                if (node & 0x78000000u) node = node - (1u << 27) + 1u;
+                if (ref_has_more(node)) node = ref_next_tri(node);
                 else RT_POP();
                 continue;
             }
@@ -717,7 +727,7 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
                 leaf_test_one<!kDeferred, kTieById>(A, q0, q1, q2, slot, o, d, nd, start_length, h, verified_ptr, &skip_twin);
                 tcut = h.t * kBestWiden;
                 const uint32_t step = skip_twin ? 2u : 1u;
-                if (((node >> 27) & 0xFu) >= step) node = node - (step << 27) + step;
+                if ((node & RT_REF_COUNT_MASK) >= step) node = ref_next_tri(node, step);
                 else RT_POP();
                 continue;
             }
@@ -725,7 +735,7 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
             else leaf_test_one<!kDeferred, kTieById>(A, q0, q1, q2, slot, o, d, nd, start_length, h, verified_ptr);
 #endif
             tcut = h.t * kBestWiden;
-            if (node & 0x78000000u) node = node - (1u << 27) + 1u;
+            if (ref_has_more(node)) node = ref_next_tri(node);
             else RT_POP();
         }
 #if RT_TW_CARRY_PERIOD > 1
@@ -735,7 +745,7 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
 #if RT_TW_LEAN
     if (kDeferred && win_slot != RT_SENTINEL)
     {   // the winner's details, once per ray: the same arithmetic on the same record gives the same t, u, v bit for bit
-        const char* rec = reinterpret_cast<const char*>(A.tris + win_slot);
+        const char* rec = A.arena + win_slot;
         const float4 q0 = ldg4(rec), q1 = ldg4(rec + 16), q2 = ldg4(rec + 32);
         float t, bu, bv;
         tri_test(o, nd, q0, q1, q2, t, bu, bv);
@@ -766,15 +776,15 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
             if (busy)
             {
                 const bool is_leaf = (node & RT_LEAF_BIT) != 0u;
-                const uint32_t slot = node & 0x07FFFFFFu;
-                const char* rec = is_leaf ? reinterpret_cast<const char*>(A.tris + slot) : reinterpret_cast<const char*>(A.wide + node);
+                const uint32_t slot = node & RT_REF_BYTE_MASK;
+                const char* rec = A.arena + slot;
                 const float4 q0 = ldg4(rec), q1 = ldg4(rec + 16), q2 = ldg4(rec + 32);
                 const uint2 q3 = __ldg(reinterpret_cast<const uint2*>(rec + 48));
                 if (!is_leaf) RT_NODE_MATH(q0, q1, q2, q3);
                 else
                 {
                     leaf_test_one<!kDeferred, kTieById>(A, q0, q1, q2, slot, o, d, nd, start_length, h, verified_ptr);
-                    if (node & 0x78000000u) node = node - (1u << 27) + 1u;
+                    if (ref_has_more(node)) node = ref_next_tri(node);
                     else RT_POP();
                 }
             }
@@ -792,8 +802,8 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
         }
         else
         {
-            leaf_tests<!kDeferred, kTieById>(A, node & 0x07FFFFFFu, 1u, o, d, nd, start_length, h, verified_ptr);
-            if (node & 0x78000000u) node = node - (1u << 27) + 1u;
+            leaf_tests<!kDeferred, kTieById>(A, ref_slot(A, node), 1u, o, d, nd, start_length, h, verified_ptr);
+            if (ref_has_more(node)) node = ref_next_tri(node);
             else RT_POP();
         }
     }
@@ -835,6 +845,10 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
         RT_LEAF_STEP(node);
         RT_POP();
     }
+#endif
+#if RT_TW_MODE == 7 || RT_TW_MODE == 8
+    // h entered as a sphere hit or a miss, so a triangle id means "found in this loop": its h.slot is still an arena byte offset
+    if (h.id != RT_MISS_ID && !(h.id & RT_SPHERE_ID_BIT)) h.slot = offset_slot(A, h.slot);
 #endif
 #undef RT_NODE_STEP
 #undef RT_NODE_MATH

@@ -13,6 +13,9 @@
 #include <cstdint>
 #include "accel.h"
 
+#ifndef RT_TW_BRANCHLESS
+#define RT_TW_BRANCHLESS 0
+#endif
 #ifndef RT_TW_SPPTR
 #define RT_TW_SPPTR 1   /* traversal stack pointer as a pointer (push = store + add, pop = load + add): 50.8 -> 50.3 ms */
 #endif
@@ -599,6 +602,17 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
             const float lo1 = fmaf(-kWiden, fabsf(mn1), mn1) - slack, hi1 = fmaf(kWiden, fabsf(mx1), mx1) + slack;          \
             hit0 = hi0 >= lo0 && lo0 <= h.t && hi0 > 0.0f;                                                                  \
             hit1 = hi1 >= lo1 && lo1 <= h.t && hi1 > 0.0f;                                                                  \
+        }                                                                                                                   \
+        if (RT_TW_BRANCHLESS && RT_TW_SPPTR && !RT_TW_TOS && !RT_TW_SHSTACK)                                               \
+        {   /* one select chain instead of three short divergent branches: the far child is stored unconditionally and kept   \
+               (pointer advanced) only when both boxes were hit; the slot above the top is always inside the array */        \
+            const bool take1 = hit1 && (!hit0 || mn1 < mn0);                                                                \
+            const uint32_t nxt = take1 ? ch.y : ch.x;                                                                       \
+            *sp_ptr = take1 ? ch.x : ch.y;                                                                                  \
+            sp_ptr += (hit0 && hit1) ? 1 : 0;                                                                               \
+            if (hit0 || hit1) node = nxt;                                                                                   \
+            else RT_POP();                                                                                                  \
+            break;                                                                                                          \
         }                                                                                                                   \
         if (hit0 && hit1)                                                                                                   \
         {                                                                                                                   \

@@ -68,6 +68,7 @@ SYMBOLS = {
     "rt_rng_draw": (_I, [_P, _U64, _U32, _P, _P]),
     "rt_accel_create": (_I, [_P, _U32, _P, _P, _U32, _P, _U32, _U32, C.POINTER(_P)]),
     "rt_accel_destroy": (_I, [_P]),
+    "rt_accel_check_host": (_I, [_P, _U32, _P, _P, _U32, _P, _U32, _U32, C.POINTER(_U64)]),
     "rt_accel_info": (_I, [_P, C.POINTER(_U64)]),
     "rt_accel_bind": (_I, [_P, _P]),
     "rt_accel_unbind": (_I, [_P]),

@@ -84,6 +84,9 @@ int BuildAccelHost(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* 
                    const RtFace* faces, uint32_t face_count, const RtVertex* vertices, uint32_t vertex_count,
                    uint32_t fat_leaf_threshold, AccelHost& out);
 
+// Host-only structural check (every slot reachable exactly once through byte-offset references, ranges, depths, leaf bookkeeping).
+int CheckAccelHost(const AccelHost& a, const RtBVHNode* nodes, uint32_t node_count, uint64_t* info4, const char** why);
+
 // Device-side view passed to kernels by value.
 struct AccelView
 {

@@ -232,3 +232,55 @@ int BuildAccelHost(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* 
     lap("byte-offset refs");
     return 0;
 }
+
+// Host-only structural check of a re-layout (no device): walks the wide tree from the root through the byte-offset references and
+// verifies what the traversal kernels rely on. Returns 0 or a negative RT_E_*; `why` receives the first violation.
+int CheckAccelHost(const AccelHost& a, const RtBVHNode* nodes, uint32_t node_count, uint64_t* info4, const char** why)
+{
+    auto fail = [&](const char* w) { if (why) *why = w; return (int)RT_E_INVALID; };
+    const uint64_t arena = (uint64_t)a.wide.size() * sizeof(WideNode) + (uint64_t)a.tris.size() * sizeof(TriRecord);
+    if (a.tri_byte0 != a.wide.size() * sizeof(WideNode)) return fail("tri_byte0 is not the end of the wide nodes");
+    std::vector<uint8_t> seen(a.tris.size(), 0);
+    std::vector<std::pair<uint32_t, uint32_t>> stack;  // (reference, depth)
+    stack.push_back({ a.root_ref, 0 });
+    uint64_t leaves = 0, inner = 0, max_depth = 0;
+    while (!stack.empty())
+    {
+        const auto [ref, depth] = stack.back(); stack.pop_back();
+        if (ref == RT_SENTINEL) return fail("sentinel used as a child reference");
+        max_depth = std::max<uint64_t>(max_depth, depth);
+        const uint32_t off = ref & RT_REF_BYTE_MASK;
+        if (ref & RT_LEAF_BIT)
+        {
+            const uint32_t count = (ref & RT_REF_COUNT_MASK) + 1u;
+            if (off < a.tri_byte0 || (off - a.tri_byte0) % sizeof(TriRecord)) return fail("leaf reference does not address a triangle record");
+            const uint64_t first = (off - a.tri_byte0) / sizeof(TriRecord);
+            if (((off - a.tri_byte0) >> 4) * 0xAAAAAAABu != (uint32_t)first) return fail("offset -> slot inverse-of-3 division is not exact");
+            if (first + count > a.tris.size() || count > RT_MAX_LEAF_PRIMS) return fail("leaf range outside the triangle records");
+            uint32_t leaf_node = a.tris[first].ref_leaf & RT_REF_LEAF_MASK;
+            for (uint64_t s = first; s < first + count; s++)
+            {
+                if (seen[s]++) return fail("slot reachable twice");
+                const TriRecord& t = a.tris[s];
+                const uint32_t rl = t.ref_leaf & RT_REF_LEAF_MASK;
+                if (rl >= node_count || nodes[rl].prim_count == 0) return fail("ref_leaf is not a reference leaf");
+                if (t.orig_slot < nodes[rl].first_index || t.orig_slot >= nodes[rl].first_index + nodes[rl].prim_count) return fail("orig_slot outside its reference leaf");
+                if (rl != leaf_node && nodes[rl].prim_count <= RT_MAX_LEAF_PRIMS && nodes[leaf_node].prim_count <= RT_MAX_LEAF_PRIMS) return fail("product leaf mixes reference leaves");
+                if ((t.ref_leaf & RT_TWIN_BIT) && s + 1 >= first + count) return fail("twin flag on the last record of a leaf");
+            }
+            leaves++;
+        }
+        else
+        {
+            if (off % sizeof(WideNode) || off >= a.tri_byte0 || (ref & RT_REF_COUNT_MASK)) return fail("inner reference does not address a wide node");
+            if (depth + 2 > RT_STACK_SIZE) return fail("deeper than the traversal stack");
+            const WideNode& w = a.wide[off / sizeof(WideNode)];
+            inner++;
+            stack.push_back({ w.child[0], depth + 1 }); stack.push_back({ w.child[1], depth + 1 });
+        }
+    }
+    for (uint8_t v : seen) if (v != 1) return fail("slot not reachable from the root");
+    if (arena + 64 > RT_REF_BYTE_MASK) return fail("arena larger than the reference range");
+    if (info4) { info4[0] = inner; info4[1] = leaves; info4[2] = max_depth; info4[3] = arena; }
+    return 0;
+}

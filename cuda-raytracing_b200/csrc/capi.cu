@@ -118,6 +118,18 @@ int rt_accel_create(const RtBVHNode* nodes, uint32_t node_count, const uint32_t*
     return RT_OK;
 }
 
+int rt_accel_check_host(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* face_indices,
+                        const RtFace* faces, uint32_t face_count, const RtVertex* vertices, uint32_t vertex_count,
+                        uint32_t fat_leaf_threshold, uint64_t* info4)
+{
+    AccelHost host;
+    if (int r = BuildAccelHost(nodes, node_count, face_indices, faces, face_count, vertices, vertex_count, fat_leaf_threshold, host))
+        return Fail(r, r == RT_E_DEPTH ? "rt_accel_check_host: BVH deeper than the traversal stack" : "rt_accel_check_host: inconsistent BVH/scene arrays");
+    const char* why = "";
+    if (int r = CheckAccelHost(host, nodes, node_count, info4, &why)) return Fail(r, std::string("rt_accel_check_host: ") + why);
+    return RT_OK;
+}
+
 int rt_accel_destroy(RtAccel* a)
 {
     if (!a) return RT_OK;

@@ -67,6 +67,11 @@ int rt_accel_create(const RtBVHNode* nodes, uint32_t node_count, const uint32_t*
                     const RtFace* faces, uint32_t face_count, const RtVertex* vertices, uint32_t vertex_count,
                     uint32_t fat_leaf_threshold, RtAccel** out);
 int rt_accel_destroy(RtAccel* accel);
+/* host only, no device: builds the same re-layout and checks its structure (every triangle slot reachable exactly once from the root
+ * through the byte-offset references, ranges, depth, leaf bookkeeping). info4 = inner nodes, product leaves, max depth, arena bytes. */
+int rt_accel_check_host(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* face_indices,
+                        const RtFace* faces, uint32_t face_count, const RtVertex* vertices, uint32_t vertex_count,
+                        uint32_t fat_leaf_threshold, uint64_t* info4);
 /* info[0..7] = wide nodes, triangle slots, reference leaves, fat leaves (low 32 bits) | adjacent duplicate-face pairs (high 32 bits),
  * max depth (wide), device bytes lo, hi, reference depth */
 int rt_accel_info(const RtAccel* accel, uint64_t* info8);

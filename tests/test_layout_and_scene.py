@@ -135,6 +135,32 @@ def test_parallel_bvh_build_adversarial_soup_vs_reference(rt, ref):
     assert a["nodes"]["prim_count"].max() >= 20000
 
 
+def test_accel_relayout_structure_on_the_host(rt, bunny):
+    """The B200 re-layout (one arena, byte-offset references, fat-leaf sub-trees) built and walked on the host, no device: every BVH slot
+    reachable exactly once from the root, references aligned and in range, leaf bookkeeping consistent - bunny scene, every fat-leaf
+    threshold, and small random soups through the reference-identical BVH builder."""
+    def check(a, threshold):
+        info = (C.c_uint64 * 4)()
+        r = rt.lib().rt_accel_check_host(rt.ptr(a["nodes"]), len(a["nodes"]), rt.ptr(a["face_indices"]), rt.ptr(a["faces"]), len(a["faces"]),
+                                         rt.ptr(a["vertices"]), len(a["vertices"]), threshold, info)
+        assert r == 0, rt.lib().rt_last_error()
+        return [int(v) for v in info]
+    a = bunny["arrays"]
+    inner, leaves, depth, arena = check(a, 0)
+    assert arena == inner * 64 + len(a["faces"]) * 48 and leaves >= 69273 and depth < 62
+    for threshold in (1, 2, 4, 16):
+        i2, l2, d2, _ = check(a, threshold)
+        assert i2 + 1 == l2 or i2 == l2 - 1  # a binary tree
+    rng = np.random.default_rng(5)
+    for n in (1, 2, 3, 17, 400):
+        scene = rt.Scene(None)
+        for _ in range(n):
+            c = rng.uniform(-10, 10, 3); e = rng.normal(size=(3, 3))
+            scene.add_triangle(*(c + e[k] for k in range(3)), 0)
+        scene.build_bvh()
+        check(scene.arrays(), 0)
+
+
 def test_golden_hashes(rt, bunny):
     """Runs everywhere (no /root/reference needed): arrays hash to what the GLM + BVH.cpp build produced."""
     h = json.load(open(os.path.join(util.GOLDEN, "scene_hashes.json")))

@@ -77,8 +77,8 @@ __device__ __forceinline__ void write_pixel(const FrameParams& P, int x, int y, 
 
 // kMode 0: product traversal. kMode 2: reference-order traversal with work counters (measurement of the
 // algorithmic bytes per ray; same image up to exact-tie resolution).
-template <int kMode, int kMinBlocks, bool kLockstep = false, bool kCount = false>
-__global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK)) pathtrace_megakernel(AccelView A, SceneView S, FrameParams P)
+template <int kMode, int kMinBlocks, bool kLockstep = false, bool kCount = false, int kMinusCtas = 0>
+__global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK) - kMinusCtas) pathtrace_megakernel(AccelView A, SceneView S, FrameParams P)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     // CTA = 16 x (RT_PT_BLOCK / 16) pixels, warp = 8 x 4. P.row_order permutes the order in which tile rows are scheduled
@@ -303,6 +303,8 @@ cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, cons
 #if RT_PT_BINNING
     else if (P.pixel_cost) pathtrace_megakernel<0, 5, false, true><<<grid, block, 0, stream>>>(accel, scene, P);
 #endif
+    else if (min_blocks == 45) pathtrace_megakernel<0, 5, false, false, 1><<<grid, block, 0, stream>>>(accel, scene, P);  // 9 CTAs of 128 threads: 56 registers
+    else if (min_blocks == 55) pathtrace_megakernel<0, 6, false, false, 1><<<grid, block, 0, stream>>>(accel, scene, P);  // 11 CTAs: 44 registers
     else if (min_blocks == 6) pathtrace_megakernel<0, 6><<<grid, block, 0, stream>>>(accel, scene, P);
     else if (min_blocks == 4) pathtrace_megakernel<0, 4><<<grid, block, 0, stream>>>(accel, scene, P);
     else if (min_blocks == 3) pathtrace_megakernel<0, 3><<<grid, block, 0, stream>>>(accel, scene, P);

@@ -37,6 +37,12 @@
 #ifndef RT_TW_TWIN
 #define RT_TW_TWIN 0   /* build switch shared by accel_build.cpp (pair + flag the copies) and traverse.cuh (skip them): measured slower, off */
 #endif
+// Wide-node boxes as centre + half extent (build switch shared by accel_build.cpp and the traversal kernels): the entry / exit
+// distance per axis is mid -/+ half * |1/d| with mid = (centre - o) / d, all on the fma pipe - no min/max per axis (ALU pipe).
+// Half extents are rounded up and inflated by 2^-21 (+ the centre's own rounding) at build time, so the stored box is a superset.
+#ifndef RT_TW_CENTER
+#define RT_TW_CENTER 1   /* 49.8 -> 46.0 ms, frame + RNG bit-identical (the ALU pipe, not the issue port, bounds the node step) */
+#endif
 #define RT_TWIN_BIT 0x80000000u
 #define RT_REF_LEAF_MASK 0x7FFFFFFFu
 #define RT_STACK_SIZE 64
@@ -47,9 +53,9 @@ struct alignas(64) WideNode
 {
     // register-pair friendly order for Blackwell's packed fp32 ops (add/mul/fma .f32x2): every aligned pair of a 128-bit load
     // is combined with one per-ray constant pair, (x, y) or (z, z)
-    RtFloat4 a;   // lo0.x lo0.y | hi0.x hi0.y
-    RtFloat4 b;   // lo1.x lo1.y | hi1.x hi1.y
-    RtFloat4 c;   // lo0.z hi0.z | lo1.z hi1.z
+    RtFloat4 a;   // lo0.x lo0.y | hi0.x hi0.y      (RT_TW_CENTER: centre0.x centre0.y | half0.x half0.y)
+    RtFloat4 b;   // lo1.x lo1.y | hi1.x hi1.y      (RT_TW_CENTER: centre1.x centre1.y | half1.x half1.y)
+    RtFloat4 c;   // lo0.z hi0.z | lo1.z hi1.z      (RT_TW_CENTER: centre0.z centre1.z | half0.z half1.z)
     uint32_t child[2];
     uint32_t pad[2];
 };

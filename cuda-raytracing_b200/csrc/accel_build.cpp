@@ -39,6 +39,22 @@ namespace
 
     inline void SetChildBox(WideNode& w, int which, const Box& b)
     {
+#if RT_TW_CENTER
+        float c[3], h[3];
+        for (int k = 0; k < 3; k++)
+        {   // [c - h, c + h] in exact arithmetic holds [lo, hi]; h carries the 2^-21 the kernel's rounding of h * |1/d| needs
+            const double lo = b.lo[k], hi = b.hi[k];
+            c[k] = (float)(0.5 * (lo + hi));
+            if (!(lo <= hi)) { c[k] = 0.0f; h[k] = -1e30f; continue; }  // empty box: exit far before entry, never hit
+            const double need = std::max(hi - (double)c[k], (double)c[k] - lo) * (1.0 + 4.8e-7) + 1e-37;
+            float hf = (float)need;
+            if ((double)hf < need) hf = std::nextafter(hf, INFINITY);
+            h[k] = hf;
+        }
+        if (which == 0) { w.a = { c[0], c[1], h[0], h[1] }; w.c.x = c[2]; w.c.z = h[2]; }
+        else { w.b = { c[0], c[1], h[0], h[1] }; w.c.y = c[2]; w.c.w = h[2]; }
+        return;
+#endif
         if (which == 0) { w.a = { b.lo[0], b.lo[1], b.hi[0], b.hi[1] }; w.c.x = b.lo[2]; w.c.y = b.hi[2]; }
         else { w.b = { b.lo[0], b.lo[1], b.hi[0], b.hi[1] }; w.c.z = b.lo[2]; w.c.w = b.hi[2]; }
     }

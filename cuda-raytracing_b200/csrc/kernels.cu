@@ -249,6 +249,22 @@ __device__ __forceinline__ void extend_inner(const AccelView& A, ExtendLane& L, 
     const WideNode* w = ref_wide(A, L.node);
     const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32);
     const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
+#if RT_TW_CENTER
+    // centre + half-extent nodes (accel.h): entry / exit = mid -/+ half * |inv| per axis, FMA form for mid (L.slack covers its cancellation)
+    const float aix = fabsf(L.ix), aiy = fabsf(L.iy), aiz = fabsf(L.iz);
+    float mid = fmaf(a.x, L.ix, L.cx), half = a.z * aix;
+    float mn0 = mid - half, mx0 = mid + half;
+    mid = fmaf(a.y, L.iy, L.cy); half = a.w * aiy;
+    mn0 = fmaxf(mn0, mid - half); mx0 = fminf(mx0, mid + half);
+    mid = fmaf(c.x, L.iz, L.cz); half = c.z * aiz;
+    mn0 = fmaxf(mn0, mid - half); mx0 = fminf(mx0, mid + half);
+    mid = fmaf(b.x, L.ix, L.cx); half = b.z * aix;
+    float mn1 = mid - half, mx1 = mid + half;
+    mid = fmaf(b.y, L.iy, L.cy); half = b.w * aiy;
+    mn1 = fmaxf(mn1, mid - half); mx1 = fminf(mx1, mid + half);
+    mid = fmaf(c.y, L.iz, L.cz); half = c.w * aiz;
+    mn1 = fmaxf(mn1, mid - half); mx1 = fminf(mx1, mid + half);
+#else
     float t1 = fmaf(a.x, L.ix, L.cx), t2 = fmaf(a.z, L.ix, L.cx);
     float mn0 = fminf(t1, t2), mx0 = fmaxf(t1, t2);
     t1 = fmaf(a.y, L.iy, L.cy); t2 = fmaf(a.w, L.iy, L.cy);
@@ -261,6 +277,7 @@ __device__ __forceinline__ void extend_inner(const AccelView& A, ExtendLane& L, 
     mnb = fminf(t1, t2); mxb = fmaxf(t1, t2);
     t1 = fmaf(c.z, L.iz, L.cz); t2 = fmaf(c.w, L.iz, L.cz);
     mn1 = fmaxf(fmaxf(mn1, mnb), fminf(t1, t2)); mx1 = fminf(fminf(mx1, mxb), fmaxf(t1, t2));
+#endif
     const float lo0 = fmaf(-kWiden, fabsf(mn0), mn0) - L.slack, hi0 = fmaf(kWiden, fabsf(mx0), mx0) + L.slack;
     const float lo1 = fmaf(-kWiden, fabsf(mn1), mn1) - L.slack, hi1 = fmaf(kWiden, fabsf(mx1), mx1) + L.slack;
     const bool hit0 = hi0 >= lo0 && lo0 <= L.h.t && hi0 > 0.0f;

@@ -354,6 +354,27 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
     }
 }
 
+#if RT_TW_CENTER
+// Entry / exit distances of both child boxes of a centre + half-extent wide node (accel.h): per axis mid = (centre - o) * inv,
+// entry = mid - half * |inv|, exit = mid + half * |inv| - twelve packed fma-pipe instructions and four 3-input min/max, no per-axis
+// min/max pair. Conservative, not exact: mid carries ~1 ulp of |mid| <= |entry| + half |inv|; the half |inv| share is covered by
+// the 2^-21 the builder adds to every half extent, the rest by the callers' relative widening (kWiden).
+__device__ __forceinline__ void center_slabs(float4 a, float4 b, float4 c, float2 no_xy, float2 no_zz, float2 i_xy, float2 i_zz,
+                                             float2 ai_xy, float2 ai_zz, float& mn0, float& mx0, float& mn1, float& mx1)
+{
+    const float2 m0 = __fmul2_rn(__fadd2_rn(make_float2(a.x, a.y), no_xy), i_xy);
+    const float2 m1 = __fmul2_rn(__fadd2_rn(make_float2(b.x, b.y), no_xy), i_xy);
+    const float2 mz = __fmul2_rn(__fadd2_rn(make_float2(c.x, c.y), no_zz), i_zz);
+    const float2 h0 = make_float2(a.z, a.w), h1 = make_float2(b.z, b.w), hz = make_float2(c.z, c.w);
+    const float2 nai_xy = make_float2(-ai_xy.x, -ai_xy.y), nai_zz = make_float2(-ai_zz.x, -ai_zz.y);
+    const float2 n0 = __ffma2_rn(h0, nai_xy, m0), f0 = __ffma2_rn(h0, ai_xy, m0);
+    const float2 n1 = __ffma2_rn(h1, nai_xy, m1), f1 = __ffma2_rn(h1, ai_xy, m1);
+    const float2 nzz = __ffma2_rn(hz, nai_zz, mz), fzz = __ffma2_rn(hz, ai_zz, mz);
+    mn0 = fmaxf(fmaxf(n0.x, n0.y), nzz.x); mx0 = fminf(fminf(f0.x, f0.y), fzz.x);
+    mn1 = fmaxf(fmaxf(n1.x, n1.y), nzz.y); mx1 = fminf(fminf(f1.x, f1.y), fzz.y);
+}
+#endif
+
 // Product traversal: wide nodes, near-child-first, while-while, conservative box culls in
 // normalised units, exact leaf box re-check only on candidate hits.
 // `h` enters holding the sphere result (or a miss with t = 1e30).
@@ -511,6 +532,9 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
     // one follows from the sign of inv (fma is monotonic in the plane), so the min/max pairs become selects: same instruction count.
     const float2 i_xy = make_float2(ix, iy), i_zz = make_float2(iz, iz), no_xy = make_float2(-o.x, -o.y), no_zz = make_float2(-o.z, -o.z);
     const float2 c_xy = make_float2(cx, cy), c_zz = make_float2(cz, cz);
+#if RT_TW_CENTER
+    const float2 ai_xy = make_float2(fabsf(ix), fabsf(iy)), ai_zz = make_float2(fabsf(iz), fabsf(iz));
+#endif
     const bool neg_x = ix < 0.0f, neg_y = iy < 0.0f, neg_z = iz < 0.0f;
     const float ex = 4.0e-7f * fabsf(ax) + 1e-30f, ey = 4.0e-7f * fabsf(ay) + 1e-30f, ez = 4.0e-7f * fabsf(az) + 1e-30f;
     const float cnx = cx - ex, cny = cy - ey, cnz = cz - ez, cfx = cx + ex, cfy = cy + ey, cfz = cz + ez;
@@ -521,6 +545,11 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
         const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));                      \
         RT_NODE_MATH(a, b, c, ch);                                                                                          \
     } while (0)
+#if RT_TW_CENTER
+#define RT_CENTER_SLABS(a, b, c) if (true) center_slabs(a, b, c, no_xy, no_zz, i_xy, i_zz, ai_xy, ai_zz, mn0, mx0, mn1, mx1); else
+#else
+#define RT_CENTER_SLABS(a, b, c)
+#endif
 #define RT_NODE_MATH(a, b, c, ch)                                                                                          \
     do {                                                                                                                    \
         if (RT_TW_PREFETCH_CHILD)                                                                                           \
@@ -549,6 +578,7 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
             break;                                                                                                          \
         }                                                                                                                   \
         float mn0, mx0, mn1, mx1;                                                                                           \
+        RT_CENTER_SLABS(a, b, c)                                                                                            \
         if (RT_TW_PACKED)                                                                                                   \
         {   /* Blackwell packed fp32: six 2-wide ops per slab stage instead of twelve scalar ones; same IEEE results */     \
             float2 d0, d1, d2, d3, d4, d5;                                                                                  \

@@ -297,6 +297,58 @@ int CheckAccelHost(const AccelHost& a, const RtBVHNode* nodes, uint32_t node_cou
     }
     for (uint8_t v : seen) if (v != 1) return fail("slot not reachable from the root");
     if (arena + 64 > RT_REF_BYTE_MASK) return fail("arena larger than the reference range");
+    // Box containment, bottom-up: the stored box of every wide-node child (lo/hi planes, or centre + half extent: RT_TW_CENTER) must
+    // hold, in exact arithmetic, the reference leaf boxes of everything below it (a fat leaf's private sub-tree: the triangles below).
+    // This is what makes the conservative node test safe to cull with; exactness is the deferred reference-leaf check's business.
+    struct DBox { double lo[3], hi[3]; };
+    bool contained = true;
+    auto bounds = [&](auto&& self, uint32_t ref) -> DBox
+    {
+        DBox b{ { 1e300, 1e300, 1e300 }, { -1e300, -1e300, -1e300 } };
+        auto grow = [&](const double* lo, const double* hi) { for (int k = 0; k < 3; k++) { b.lo[k] = std::min(b.lo[k], lo[k]); b.hi[k] = std::max(b.hi[k], hi[k]); } };
+        const uint32_t off = ref & RT_REF_BYTE_MASK;
+        if (ref & RT_LEAF_BIT)
+        {
+            const uint32_t count = (ref & RT_REF_COUNT_MASK) + 1u;
+            const uint64_t first = (off - a.tri_byte0) / sizeof(TriRecord);
+            const RtBVHNode& rn = nodes[a.tris[first].ref_leaf & RT_REF_LEAF_MASK];
+            if (rn.prim_count == count)
+            {
+                const double lo[3] = { rn.bounds_min.x, rn.bounds_min.y, rn.bounds_min.z }, hi[3] = { rn.bounds_max.x, rn.bounds_max.y, rn.bounds_max.z };
+                grow(lo, hi);
+            }
+            else
+                for (uint64_t s = first; s < first + count; s++)
+                {
+                    const TriRecord& t = a.tris[s];
+                    for (int v = 0; v < 3; v++)
+                    {
+                        double p[3];
+                        for (int k = 0; k < 3; k++) p[k] = (double)t.v0[k] + (v == 1 ? (double)t.e1[k] : v == 2 ? (double)t.e2[k] : 0.0);
+                        grow(p, p);
+                    }
+                }
+            return b;
+        }
+        const WideNode& w = a.wide[off / sizeof(WideNode)];
+        for (int c = 0; c < 2; c++)
+        {
+            const DBox cb = self(self, w.child[c]);
+            const RtFloat4& q = c == 0 ? w.a : w.b;
+            double lo[3], hi[3];
+#if RT_TW_CENTER
+            const double ctr[3] = { q.x, q.y, c == 0 ? w.c.x : w.c.y }, half[3] = { q.z, q.w, c == 0 ? w.c.z : w.c.w };
+            for (int k = 0; k < 3; k++) { lo[k] = ctr[k] - half[k]; hi[k] = ctr[k] + half[k]; }
+#else
+            lo[0] = q.x; lo[1] = q.y; hi[0] = q.z; hi[1] = q.w; lo[2] = c == 0 ? w.c.x : w.c.z; hi[2] = c == 0 ? w.c.y : w.c.w;
+#endif
+            for (int k = 0; k < 3; k++) if (!(lo[k] <= cb.lo[k] && hi[k] >= cb.hi[k])) contained = false;
+            grow(cb.lo, cb.hi);
+        }
+        return b;
+    };
+    bounds(bounds, a.root_ref);
+    if (!contained) return fail("a wide-node child box does not contain the reference boxes below it");
     if (info4) { info4[0] = inner; info4[1] = leaves; info4[2] = max_depth; info4[3] = arena; }
     return 0;
 }

@@ -141,8 +141,9 @@ def test_parallel_bvh_build_adversarial_soup_vs_reference(rt, ref):
 
 def test_accel_relayout_structure_on_the_host(rt, bunny):
     """The B200 re-layout (one arena, byte-offset references, fat-leaf sub-trees) built and walked on the host, no device: every BVH slot
-    reachable exactly once from the root, references aligned and in range, leaf bookkeeping consistent - bunny scene, every fat-leaf
-    threshold, and small random soups through the reference-identical BVH builder."""
+    reachable exactly once from the root, references aligned and in range, leaf bookkeeping consistent, and every wide-node child box
+    (centre + half extent) holding, in exact arithmetic, the reference leaf boxes / triangles below it (what makes the conservative node
+    test safe) - bunny scene, every fat-leaf threshold, and small random soups through the reference-identical BVH builder."""
     def check(a, threshold):
         info = (C.c_uint64 * 4)()
         r = rt.lib().rt_accel_check_host(rt.ptr(a["nodes"]), len(a["nodes"]), rt.ptr(a["face_indices"]), rt.ptr(a["faces"]), len(a["faces"]),

@@ -1,0 +1,39 @@
+"""Rewrite profiles/traffic.json from an `ncu --set full` report of one pathtrace_megakernel launch (run where ncu is installed):
+    python benchmarks/update_traffic.py gpurun_out/X.ncu-rep "source note"
+bench.py reads the DRAM bytes and the warp-instruction count of the dominant kernel from that file (roofline.traffic / roofline.issue)."""
+import csv
+import io
+import json
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def main(rep, note):
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    hdr, units = rows[0], rows[1]
+    d = dict(zip(hdr, rows[2]))
+    assert "pathtrace_megakernel" in d["Kernel Name"], d["Kernel Name"]
+
+    def val(key):
+        v = float(d[key].replace(",", ""))
+        u = units[hdr.index(key)].lower()
+        return v * {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9}.get(u, 1)
+
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    t = json.load(open(path))
+    t["pathtrace_megakernel"] = {
+        "dram_bytes_per_launch": int(val("dram__bytes_read.sum") + val("dram__bytes_write.sum")),
+        "warp_instructions_per_launch": int(val("smsp__inst_executed.sum")),
+        "threads_per_instruction": round(val("smsp__thread_inst_executed_per_inst_executed.ratio"), 2),
+        "source": note,
+    }
+    json.dump(t, open(path, "w"), indent=1)
+    print(json.dumps(t["pathtrace_megakernel"]))
+
+
+if __name__ == "__main__":
+    main(sys.argv[1], sys.argv[2] if len(sys.argv) > 2 else os.path.basename(sys.argv[1]))

@@ -25,6 +25,9 @@
 #ifndef RT_TW_TRI_PACKED
 #define RT_TW_TRI_PACKED 1   /* tri_test in packed fp32 (FMUL2 / FADD2), bit-identical: 52.9 -> 51.3 ms */
 #endif
+#ifndef RT_TW_TRI_SIGNFLIP
+#define RT_TW_TRI_SIGNFLIP 1   /* one sign-free miss test instead of two divergent sign cases, bit-identical: 45.95 -> 45.02 ms */
+#endif
 #ifndef RT_TW_TRI_STAGED
 #define RT_TW_TRI_STAGED 0   /* tri_test: u range test before the second triple product is evaluated: one more divergent branch, 54.9 vs 52.9 ms, off */
 #endif
@@ -200,6 +203,17 @@ __device__ __forceinline__ bool tri_test(Vec3 o, Vec3 nd, float4 r0, float4 r1, 
         const float qz = qb.y - qb.x;
         const float2 vv = __fmul2_rn(nd_xy, qxy);
         const float v = (vv.x + vv.y) + nd.z * qz;
+#if RT_TW_TRI_SIGNFLIP
+        {   // GLM's two sign cases (intersect.inl:44-63) as one: for det < 0 its tests are the det > 0 tests of (-u, -v, -(u + v))
+            // against -det, and flipping a sign bit is exact - same decisions (NaNs included), no data-dependent branch on the sign
+            // of det (lanes of a warp see front and back faces mixed: the two cases used to run one after the other)
+            const uint32_t flip = __float_as_uint(det) & 0x80000000u;
+            const float ad = fabsf(det);
+            const float us = __uint_as_float(__float_as_uint(u) ^ flip), vs = __uint_as_float(__float_as_uint(v) ^ flip);
+            const float uvs = __uint_as_float(__float_as_uint(u + v) ^ flip);
+            if (!(ad > FLT_EPSILON) || (us < 0.0f || us > ad) || (vs < 0.0f || uvs > ad)) return false;
+        }
+#else
         if (det > FLT_EPSILON)
         {
             if (u < 0.0f || u > det) return false;
@@ -211,6 +225,7 @@ __device__ __forceinline__ bool tri_test(Vec3 o, Vec3 nd, float4 r0, float4 r1, 
             if (v > 0.0f || (u + v) < det) return false;
         }
         else return false;
+#endif
         const float inv_det = 1.0f / det;
         const float2 tt = __fmul2_rn(e2xy, qxy);
         t = ((tt.x + tt.y) + r2.z * qz) * inv_det;

@@ -349,6 +349,66 @@ int CheckAccelHost(const AccelHost& a, const RtBVHNode* nodes, uint32_t node_cou
     };
     bounds(bounds, a.root_ref);
     if (!contained) return fail("a wide-node child box does not contain the reference boxes below it");
+#if RT_TW_CENTER
+    // The node test itself, replayed on the host in the kernel's own fp32 arithmetic (traverse.cuh center_slabs + the relative widening:
+    // float subtract, float multiply, fmaf - this file is compiled with -ffp-contract=off): rays that hit what lies below a child, by an
+    // exact double-precision slab test of the contained bounds, must pass it. Deterministic sample of children, rays from near, far, and
+    // from points on the box faces, towards points inside the contained bounds.
+    {
+        uint64_t rng = 0x9E3779B97F4A7C15ull;
+        auto uni = [&]() { rng = rng * 6364136223846793005ull + 1442695040888963407ull; return (double)(rng >> 11) * (1.0 / 9007199254740992.0); };
+        const size_t stride = std::max<size_t>(1, a.wide.size() / 4096);
+        const float kWiden = 1.0e-6f;
+        for (size_t wi = 0; wi < a.wide.size() && a.root_ref != RT_SENTINEL && !(a.root_ref & RT_LEAF_BIT); wi += stride)
+        {
+            const WideNode& w = a.wide[wi];
+            for (int c = 0; c < 2; c++)
+            {
+                const DBox cb = bounds(bounds, w.child[c]);
+                const RtFloat4& q = c == 0 ? w.a : w.b;
+                const float ctr[3] = { q.x, q.y, c == 0 ? w.c.x : w.c.y }, half[3] = { q.z, q.w, c == 0 ? w.c.z : w.c.w };
+                double ext = 1e-6;
+                for (int k = 0; k < 3; k++) ext = std::max(ext, cb.hi[k] - cb.lo[k]);
+                for (int r = 0; r < 12; r++)
+                {
+                    double target[3], od[3];
+                    for (int k = 0; k < 3; k++) target[k] = cb.lo[k] + (cb.hi[k] - cb.lo[k]) * (0.05 + 0.9 * uni());
+                    const double reach = r < 4 ? 0.6 * ext : r < 8 ? 40.0 * ext : 3000.0 * ext;
+                    for (int k = 0; k < 3; k++) od[k] = target[k] + (2.0 * uni() - 1.0) * reach;
+                    if (r % 4 == 3) { const int k = (int)(uni() * 3.0) % 3; od[k] = uni() < 0.5 ? cb.lo[k] : cb.hi[k]; }  // origin on a face plane
+                    float o[3], d[3];
+                    double len = 0;
+                    for (int k = 0; k < 3; k++) { o[k] = (float)od[k]; len += (target[k] - o[k]) * (target[k] - o[k]); }
+                    if (!(len > 0)) continue;
+                    for (int k = 0; k < 3; k++) d[k] = (float)((target[k] - o[k]) / std::sqrt(len));
+                    if (r % 6 == 5) d[(int)(uni() * 3.0) % 3] = 0.0f;  // axis-parallel component
+                    // ground truth: exact slabs of the contained bounds for the ray (o, d) as the kernel sees it
+                    double t0 = 0.0, t1 = 1e300;
+                    bool truth = true;
+                    for (int k = 0; k < 3 && truth; k++)
+                    {
+                        if (d[k] == 0.0f) { truth = (double)o[k] >= cb.lo[k] && (double)o[k] <= cb.hi[k]; continue; }
+                        const double ta = (cb.lo[k] - o[k]) / d[k], tb = (cb.hi[k] - o[k]) / d[k];
+                        t0 = std::max(t0, std::min(ta, tb)); t1 = std::min(t1, std::max(ta, tb));
+                    }
+                    if (!truth || !(t0 <= t1)) continue;
+                    // the kernel's test
+                    float mn = -INFINITY, mx = INFINITY;
+                    for (int k = 0; k < 3; k++)
+                    {
+                        const float inv = d[k] != 0.0f ? 1.0f / d[k] : 1e30f;
+                        const float diff = ctr[k] - o[k];
+                        const float mid = diff * inv;
+                        mn = std::fmax(mn, std::fmaf(half[k], -std::fabs(inv), mid));
+                        mx = std::fmin(mx, std::fmaf(half[k], std::fabs(inv), mid));
+                    }
+                    const float lo = std::fmaf(-kWiden, std::fabs(mn), mn), hi = std::fmaf(kWiden, std::fabs(mx), mx);
+                    if (!(hi >= lo && lo <= 1e30f && hi > 0.0f)) return fail("the centre + half-extent node test rejects a ray that hits the bounds below the child");
+                }
+            }
+        }
+    }
+#endif
     if (info4) { info4[0] = inner; info4[1] = leaves; info4[2] = max_depth; info4[3] = arena; }
     return 0;
 }

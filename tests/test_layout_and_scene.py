@@ -143,7 +143,8 @@ def test_accel_relayout_structure_on_the_host(rt, bunny):
     """The B200 re-layout (one arena, byte-offset references, fat-leaf sub-trees) built and walked on the host, no device: every BVH slot
     reachable exactly once from the root, references aligned and in range, leaf bookkeeping consistent, and every wide-node child box
     (centre + half extent) holding, in exact arithmetic, the reference leaf boxes / triangles below it (what makes the conservative node
-    test safe) - bunny scene, every fat-leaf threshold, and small random soups through the reference-identical BVH builder."""
+    test safe), plus a replay of the kernel's own fp32 node test on sampled rays that hit those bounds by an exact double-precision slab
+    test: none may be rejected (with the builder's and the kernel's margins removed the replay does find rejected hits) - bunny scene, every fat-leaf threshold, and small random soups through the reference-identical BVH builder."""
     def check(a, threshold):
         info = (C.c_uint64 * 4)()
         r = rt.lib().rt_accel_check_host(rt.ptr(a["nodes"]), len(a["nodes"]), rt.ptr(a["face_indices"]), rt.ptr(a["faces"]), len(a["faces"]),

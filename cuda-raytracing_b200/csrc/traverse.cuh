@@ -25,6 +25,11 @@
 #ifndef RT_TW_TRI_PACKED
 #define RT_TW_TRI_PACKED 1   /* tri_test in packed fp32 (FMUL2 / FADD2), bit-identical: 52.9 -> 51.3 ms */
 #endif
+#ifndef RT_TW_STOPREF
+#define RT_TW_STOPREF 0   /* mode 7, NOT MEASURED yet (round-2 candidate): the end-of-ray marker is a valid leaf-flagged reference (offset 0), so the
+                             loop needs no sentinel compare per iteration - only triangle-side iterations check for it; costs one extra fetch per ray */
+#endif
+#define RT_STOP_REF RT_LEAF_BIT
 #ifndef RT_TW_TRI_SIGNFLIP
 #define RT_TW_TRI_SIGNFLIP 1   /* one sign-free miss test instead of two divergent sign cases, bit-identical: 45.95 -> 45.02 ms */
 #endif
@@ -490,7 +495,7 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
     uint32_t* const stack = carry ? carry->stack : local_stack;
     int sp = 0;
 #if !RT_TW_SHSTACK
-    stack[sp++] = RT_SENTINEL;
+    stack[sp++] = (RT_TW_STOPREF && RT_TW_MODE == 7) ? RT_STOP_REF : RT_SENTINEL;
 #endif
 #if RT_TW_TOS
     uint32_t tos = RT_SENTINEL;
@@ -729,7 +734,15 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
 #if RT_TW_LEAN
     uint32_t win_slot = RT_SENTINEL, win_key = 0u;  // kDeferred only: the best TRIANGLE so far (h.t follows; id/slot/key/u/v of h stay the entry's until the end)
 #endif
+#if RT_TW_STOPREF
+#if RT_TW_SHSTACK || RT_TW_CARRY_PERIOD != 1
+#error "RT_TW_STOPREF: only with the local-memory stack and without the unrolled suspend vote"
+#endif
+    if (node == RT_SENTINEL) node = RT_STOP_REF;  // empty scene
+    for (;;)
+#else
     while (node != RT_SENTINEL)
+#endif
     {
         if (carry && __popc(__activemask()) <= carry_limit)
         {
@@ -762,6 +775,9 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
         if (!is_leaf) RT_NODE_MATH(q0, q1, q2, q3);
         else
         {
+#if RT_TW_STOPREF
+            if (node == RT_STOP_REF) break;  // popped the stack bottom (the fetch above read the first wide node: valid memory, unused)
+#endif
 #if RT_TW_LEAN
             if (kDeferred)
             {

@@ -49,6 +49,27 @@
 
 struct RtFloat4 { float x, y, z, w; };
 
+// 48-byte wide node (RT_TW_NODE48, needs RT_TW_CENTER; round-2 candidate, NOT MEASURED): the same three 128-bit loads as a triangle
+// record and no fourth. Centres stay fp32, the six half extents are bf16 ROUNDED UP, two per word; the kernel uses the high one as the
+// word stands (the other value's bits in its low mantissa only enlarge it) and the low one as word << 16 (fma pipe).
+#ifndef RT_TW_NODE48
+#define RT_TW_NODE48 0
+#endif
+#if RT_TW_NODE48 && !RT_TW_CENTER
+#error "RT_TW_NODE48 stores centre + half extent boxes"
+#endif
+#if RT_TW_NODE48
+struct alignas(16) WideNode
+{
+    RtFloat4 a;          // centre0.x centre0.y | centre1.x centre1.y
+    float cz[2];         // centre0.z centre1.z
+    uint32_t hxy[2];     // per child: bf16(half.x) | bf16(half.y) << 16
+    uint32_t hz;         // bf16(half0.z) | bf16(half1.z) << 16
+    uint32_t child[2];
+    uint32_t pad;
+};
+static_assert(sizeof(WideNode) == 48, "WideNode layout");
+#else
 struct alignas(64) WideNode
 {
     // register-pair friendly order for Blackwell's packed fp32 ops (add/mul/fma .f32x2): every aligned pair of a 128-bit load
@@ -59,6 +80,7 @@ struct alignas(64) WideNode
     uint32_t child[2];
     uint32_t pad[2];
 };
+#endif
 
 struct alignas(16) TriRecord
 {

@@ -37,6 +37,23 @@ namespace
 
     inline uint32_t LeafRef(uint32_t first, uint32_t count) { return RT_LEAF_BIT | ((count - 1u) << 27) | first; }
 
+#if RT_TW_CENTER
+    // centre and half extent of child `which` exactly as the kernels read them (traverse.cuh center_slabs)
+    inline void ChildCentreHalf(const WideNode& w, int which, float ctr[3], float half[3])
+    {
+#if RT_TW_NODE48
+        auto as_float = [](uint32_t bits) { float v; std::memcpy(&v, &bits, 4); return v; };
+        ctr[0] = which == 0 ? w.a.x : w.a.z; ctr[1] = which == 0 ? w.a.y : w.a.w; ctr[2] = w.cz[which];
+        half[0] = as_float(w.hxy[which] << 16); half[1] = as_float(w.hxy[which]);   // the high value keeps the low one's bits in its mantissa
+        half[2] = which == 0 ? as_float(w.hz << 16) : as_float(w.hz);
+#else
+        const RtFloat4& q = which == 0 ? w.a : w.b;
+        ctr[0] = q.x; ctr[1] = q.y; ctr[2] = which == 0 ? w.c.x : w.c.y;
+        half[0] = q.z; half[1] = q.w; half[2] = which == 0 ? w.c.z : w.c.w;
+#endif
+    }
+#endif
+
     inline void SetChildBox(WideNode& w, int which, const Box& b)
     {
 #if RT_TW_CENTER
@@ -51,12 +68,25 @@ namespace
             if ((double)hf < need) hf = std::nextafter(hf, INFINITY);
             h[k] = hf;
         }
+#if RT_TW_NODE48
+        auto bf16_up = [](float v) -> uint32_t
+        {   // smallest bf16 >= v for positive finite v; the empty-box marker (negative) is truncated (still hugely negative)
+            uint32_t bits; std::memcpy(&bits, &v, 4);
+            if (!(bits & 0x80000000u) && (bits & 0xFFFFu) && (bits >> 23) != 0xFFu) bits += 0x10000u;
+            return bits >> 16;
+        };
+        if (which == 0) { w.a.x = c[0]; w.a.y = c[1]; } else { w.a.z = c[0]; w.a.w = c[1]; }
+        w.cz[which] = c[2];
+        w.hxy[which] = bf16_up(h[0]) | (bf16_up(h[1]) << 16);
+        w.hz = which == 0 ? ((w.hz & 0xFFFF0000u) | bf16_up(h[2])) : ((w.hz & 0x0000FFFFu) | (bf16_up(h[2]) << 16));
+#else
         if (which == 0) { w.a = { c[0], c[1], h[0], h[1] }; w.c.x = c[2]; w.c.z = h[2]; }
         else { w.b = { c[0], c[1], h[0], h[1] }; w.c.y = c[2]; w.c.w = h[2]; }
-        return;
 #endif
+#else
         if (which == 0) { w.a = { b.lo[0], b.lo[1], b.hi[0], b.hi[1] }; w.c.x = b.lo[2]; w.c.y = b.hi[2]; }
         else { w.b = { b.lo[0], b.lo[1], b.hi[0], b.hi[1] }; w.c.z = b.lo[2]; w.c.w = b.hi[2]; }
+#endif
     }
 
     struct Builder
@@ -334,12 +364,13 @@ int CheckAccelHost(const AccelHost& a, const RtBVHNode* nodes, uint32_t node_cou
         for (int c = 0; c < 2; c++)
         {
             const DBox cb = self(self, w.child[c]);
-            const RtFloat4& q = c == 0 ? w.a : w.b;
             double lo[3], hi[3];
 #if RT_TW_CENTER
-            const double ctr[3] = { q.x, q.y, c == 0 ? w.c.x : w.c.y }, half[3] = { q.z, q.w, c == 0 ? w.c.z : w.c.w };
-            for (int k = 0; k < 3; k++) { lo[k] = ctr[k] - half[k]; hi[k] = ctr[k] + half[k]; }
+            float ctr[3], half[3];
+            ChildCentreHalf(w, c, ctr, half);
+            for (int k = 0; k < 3; k++) { lo[k] = (double)ctr[k] - (double)half[k]; hi[k] = (double)ctr[k] + (double)half[k]; }
 #else
+            const RtFloat4& q = c == 0 ? w.a : w.b;
             lo[0] = q.x; lo[1] = q.y; hi[0] = q.z; hi[1] = q.w; lo[2] = c == 0 ? w.c.x : w.c.z; hi[2] = c == 0 ? w.c.y : w.c.w;
 #endif
             for (int k = 0; k < 3; k++) if (!(lo[k] <= cb.lo[k] && hi[k] >= cb.hi[k])) contained = false;
@@ -365,8 +396,8 @@ int CheckAccelHost(const AccelHost& a, const RtBVHNode* nodes, uint32_t node_cou
             for (int c = 0; c < 2; c++)
             {
                 const DBox cb = bounds(bounds, w.child[c]);
-                const RtFloat4& q = c == 0 ? w.a : w.b;
-                const float ctr[3] = { q.x, q.y, c == 0 ? w.c.x : w.c.y }, half[3] = { q.z, q.w, c == 0 ? w.c.z : w.c.w };
+                float ctr[3], half[3];
+                ChildCentreHalf(w, c, ctr, half);
                 double ext = 1e-6;
                 for (int k = 0; k < 3; k++) ext = std::max(ext, cb.hi[k] - cb.lo[k]);
                 for (int r = 0; r < 12; r++)

@@ -248,8 +248,13 @@ __device__ __forceinline__ void extend_inner(const AccelView& A, ExtendLane& L, 
     const float kWiden = 1.0e-6f;
     const WideNode* w = ref_wide(A, L.node);
     const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32);
+#if RT_TW_NODE48
+    const uint2 ch = make_uint2(__float_as_uint(c.y), __float_as_uint(c.z));
+    float mn0, mx0, mn1, mx1;
+    center_slabs(a, b, c, make_float2(-L.o.x, -L.o.y), make_float2(-L.o.z, -L.o.z), make_float2(L.ix, L.iy), make_float2(L.iz, L.iz),
+                 make_float2(fabsf(L.ix), fabsf(L.iy)), make_float2(fabsf(L.iz), fabsf(L.iz)), mn0, mx0, mn1, mx1);
+#elif RT_TW_CENTER
     const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
-#if RT_TW_CENTER
     // centre + half-extent nodes (accel.h): entry / exit = mid -/+ half * |inv| per axis, FMA form for mid (L.slack covers its cancellation)
     const float aix = fabsf(L.ix), aiy = fabsf(L.iy), aiz = fabsf(L.iz);
     float mid = fmaf(a.x, L.ix, L.cx), half = a.z * aix;
@@ -265,6 +270,7 @@ __device__ __forceinline__ void extend_inner(const AccelView& A, ExtendLane& L, 
     mid = fmaf(c.y, L.iz, L.cz); half = c.w * aiz;
     mn1 = fmaxf(mn1, mid - half); mx1 = fminf(mx1, mid + half);
 #else
+    const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
     float t1 = fmaf(a.x, L.ix, L.cx), t2 = fmaf(a.z, L.ix, L.cx);
     float mn0 = fminf(t1, t2), mx0 = fmaxf(t1, t2);
     t1 = fmaf(a.y, L.iy, L.cy); t2 = fmaf(a.w, L.iy, L.cy);

@@ -180,7 +180,7 @@ __global__ void __launch_bounds__(256, kMinBlocks) pathtrace_regroup_kernel(Acce
         {
             const WideNode* w = ref_wide(A, node);
             const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32);
-            const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
+            const uint2 ch = RT_TW_NODE48 ? make_uint2(__float_as_uint(c.y), __float_as_uint(c.z)) : __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
             // exact slab form (plane - o) * inv in packed fp32, three-compare conservative cull (traverse.cuh)
 #if RT_TW_CENTER
             float mn0, mx0, mn1, mx1;

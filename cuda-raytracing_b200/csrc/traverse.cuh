@@ -382,10 +382,21 @@ __device__ __forceinline__ void leaf_tests(const AccelView& A, uint32_t first, u
 __device__ __forceinline__ void center_slabs(float4 a, float4 b, float4 c, float2 no_xy, float2 no_zz, float2 i_xy, float2 i_zz,
                                              float2 ai_xy, float2 ai_zz, float& mn0, float& mx0, float& mn1, float& mx1)
 {
+#if RT_TW_NODE48
+    // 48-byte node (accel.h): a = centre0.xy centre1.xy, b = centre0.z centre1.z | two half-extent words, c.x = the z half-extent word
+    // (c.y, c.z = child references). Of each word the high bf16 is used as the word stands, the low one as word << 16.
+    const float2 m0 = __fmul2_rn(__fadd2_rn(make_float2(a.x, a.y), no_xy), i_xy);
+    const float2 m1 = __fmul2_rn(__fadd2_rn(make_float2(a.z, a.w), no_xy), i_xy);
+    const float2 mz = __fmul2_rn(__fadd2_rn(make_float2(b.x, b.y), no_zz), i_zz);
+    const float2 h0 = make_float2(__uint_as_float(__float_as_uint(b.z) << 16), b.z);
+    const float2 h1 = make_float2(__uint_as_float(__float_as_uint(b.w) << 16), b.w);
+    const float2 hz = make_float2(__uint_as_float(__float_as_uint(c.x) << 16), c.x);
+#else
     const float2 m0 = __fmul2_rn(__fadd2_rn(make_float2(a.x, a.y), no_xy), i_xy);
     const float2 m1 = __fmul2_rn(__fadd2_rn(make_float2(b.x, b.y), no_xy), i_xy);
     const float2 mz = __fmul2_rn(__fadd2_rn(make_float2(c.x, c.y), no_zz), i_zz);
     const float2 h0 = make_float2(a.z, a.w), h1 = make_float2(b.z, b.w), hz = make_float2(c.z, c.w);
+#endif
     const float2 nai_xy = make_float2(-ai_xy.x, -ai_xy.y), nai_zz = make_float2(-ai_zz.x, -ai_zz.y);
     const float2 n0 = __ffma2_rn(h0, nai_xy, m0), f0 = __ffma2_rn(h0, ai_xy, m0);
     const float2 n1 = __ffma2_rn(h1, nai_xy, m1), f1 = __ffma2_rn(h1, ai_xy, m1);
@@ -562,7 +573,8 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
     do {                                                                                                                    \
         const WideNode* w = ref_wide(A, node);                                                                              \
         const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32); \
-        const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));                      \
+        const uint2 ch = RT_TW_NODE48 ? make_uint2(__float_as_uint(c.y), __float_as_uint(c.z))                              \
+                                      : __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));       \
         RT_NODE_MATH(a, b, c, ch);                                                                                          \
     } while (0)
 #if RT_TW_CENTER
@@ -764,7 +776,11 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
         const uint32_t slot = node & RT_REF_BYTE_MASK;  // arena byte offset; a winner's h.slot is converted to its slot after the loop
         const char* rec = A.arena + slot;                // one address form for wide nodes and triangle records
         const float4 q0 = ldg4(rec), q1 = ldg4(rec + 16), q2 = ldg4(rec + 32);
+#if RT_TW_NODE48
+        const uint2 q3 = make_uint2(__float_as_uint(q2.y), __float_as_uint(q2.z));  // 48 bytes for either kind: no fourth load
+#else
         const uint2 q3 = __ldg(reinterpret_cast<const uint2*>(rec + 48));
+#endif
 #if RT_TW_PREFETCH
         if (is_leaf && ref_has_more(node))
         {   // the next record of this leaf is the next iteration's fetch: start it now (matters when the scene is not L2-resident)
@@ -854,7 +870,7 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
                 const uint32_t slot = node & RT_REF_BYTE_MASK;
                 const char* rec = A.arena + slot;
                 const float4 q0 = ldg4(rec), q1 = ldg4(rec + 16), q2 = ldg4(rec + 32);
-                const uint2 q3 = __ldg(reinterpret_cast<const uint2*>(rec + 48));
+                const uint2 q3 = RT_TW_NODE48 ? make_uint2(__float_as_uint(q2.y), __float_as_uint(q2.z)) : __ldg(reinterpret_cast<const uint2*>(rec + 48));
                 if (!is_leaf) RT_NODE_MATH(q0, q1, q2, q3);
                 else
                 {

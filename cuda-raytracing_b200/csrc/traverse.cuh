@@ -397,10 +397,18 @@ __device__ __forceinline__ void center_slabs(float4 a, float4 b, float4 c, float
     const float2 mz = __fmul2_rn(__fadd2_rn(make_float2(c.x, c.y), no_zz), i_zz);
     const float2 h0 = make_float2(a.z, a.w), h1 = make_float2(b.z, b.w), hz = make_float2(c.z, c.w);
 #endif
+#if RT_TW_NODE48 == 2
+    // scalar fmas for the half-extent products: the decoded halves do not sit in aligned register pairs, and assembling the pairs costs
+    // six moves per node step (same fma-pipe time either way)
+    const float2 n0 = make_float2(fmaf(h0.x, -ai_xy.x, m0.x), fmaf(h0.y, -ai_xy.y, m0.y)), f0 = make_float2(fmaf(h0.x, ai_xy.x, m0.x), fmaf(h0.y, ai_xy.y, m0.y));
+    const float2 n1 = make_float2(fmaf(h1.x, -ai_xy.x, m1.x), fmaf(h1.y, -ai_xy.y, m1.y)), f1 = make_float2(fmaf(h1.x, ai_xy.x, m1.x), fmaf(h1.y, ai_xy.y, m1.y));
+    const float2 nzz = make_float2(fmaf(hz.x, -ai_zz.x, mz.x), fmaf(hz.y, -ai_zz.y, mz.y)), fzz = make_float2(fmaf(hz.x, ai_zz.x, mz.x), fmaf(hz.y, ai_zz.y, mz.y));
+#else
     const float2 nai_xy = make_float2(-ai_xy.x, -ai_xy.y), nai_zz = make_float2(-ai_zz.x, -ai_zz.y);
     const float2 n0 = __ffma2_rn(h0, nai_xy, m0), f0 = __ffma2_rn(h0, ai_xy, m0);
     const float2 n1 = __ffma2_rn(h1, nai_xy, m1), f1 = __ffma2_rn(h1, ai_xy, m1);
     const float2 nzz = __ffma2_rn(hz, nai_zz, mz), fzz = __ffma2_rn(hz, ai_zz, mz);
+#endif
     mn0 = fmaxf(fmaxf(n0.x, n0.y), nzz.x); mx0 = fminf(fminf(f0.x, f0.y), fzz.x);
     mn1 = fmaxf(fmaxf(n1.x, n1.y), nzz.y); mx1 = fminf(fminf(f1.x, f1.y), fzz.y);
 }

@@ -516,6 +516,9 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
 #if !RT_TW_SHSTACK
     stack[sp++] = (RT_TW_STOPREF && RT_TW_MODE == 7) ? RT_STOP_REF : RT_SENTINEL;
 #endif
+#if RT_TW_TOS || RT_TW_SHSTACK || !RT_TW_SPPTR
+    uint32_t* sp_ptr = nullptr; (void)sp_ptr;  // only the pointer-stack form uses it; the (compiled-out) branchless block of RT_NODE_MATH names it
+#endif
 #if RT_TW_TOS
     uint32_t tos = RT_SENTINEL;
 #define RT_PUSH(x) do { stack[sp++] = tos; tos = (x); } while (0)

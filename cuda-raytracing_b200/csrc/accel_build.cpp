@@ -423,18 +423,23 @@ int CheckAccelHost(const AccelHost& a, const RtBVHNode* nodes, uint32_t node_cou
                         t0 = std::max(t0, std::min(ta, tb)); t1 = std::min(t1, std::max(ta, tb));
                     }
                     if (!truth || !(t0 <= t1)) continue;
-                    // the kernel's test
-                    float mn = -INFINITY, mx = INFINITY;
-                    for (int k = 0; k < 3; k++)
+                    // the kernel's test, with the reciprocal direction as IEEE gives it and 2 ulp to either side (room for an
+                    // approximate reciprocal, RT_TW_RCP_APPROX)
+                    for (int variant = 0; variant < 3; variant++)
                     {
-                        const float inv = d[k] != 0.0f ? 1.0f / d[k] : 1e30f;
-                        const float diff = ctr[k] - o[k];
-                        const float mid = diff * inv;
-                        mn = std::fmax(mn, std::fmaf(half[k], -std::fabs(inv), mid));
-                        mx = std::fmin(mx, std::fmaf(half[k], std::fabs(inv), mid));
+                        const float scale = variant == 0 ? 1.0f : variant == 1 ? 1.0f + 2.4e-7f : 1.0f - 2.4e-7f;
+                        float mn = -INFINITY, mx = INFINITY;
+                        for (int k = 0; k < 3; k++)
+                        {
+                            const float inv = d[k] != 0.0f ? (1.0f / d[k]) * scale : 1e30f;
+                            const float diff = ctr[k] - o[k];
+                            const float mid = diff * inv;
+                            mn = std::fmax(mn, std::fmaf(half[k], -std::fabs(inv), mid));
+                            mx = std::fmin(mx, std::fmaf(half[k], std::fabs(inv), mid));
+                        }
+                        const float lo = std::fmaf(-kWiden, std::fabs(mn), mn), hi = std::fmaf(kWiden, std::fabs(mx), mx);
+                        if (!(hi >= lo && lo <= 1e30f && hi > 0.0f)) return fail("the centre + half-extent node test rejects a ray that hits the bounds below the child");
                     }
-                    const float lo = std::fmaf(-kWiden, std::fabs(mn), mn), hi = std::fmaf(kWiden, std::fabs(mx), mx);
-                    if (!(hi >= lo && lo <= 1e30f && hi > 0.0f)) return fail("the centre + half-extent node test rejects a ray that hits the bounds below the child");
                 }
             }
         }

@@ -25,6 +25,9 @@
 #ifndef RT_TW_TRI_PACKED
 #define RT_TW_TRI_PACKED 1   /* tri_test in packed fp32 (FMUL2 / FADD2), bit-identical: 52.9 -> 51.3 ms */
 #endif
+#ifndef RT_TW_RCP_APPROX
+#define RT_TW_RCP_APPROX 0
+#endif
 #ifndef RT_TW_STOPREF
 #define RT_TW_STOPREF 0   /* mode 7, NOT MEASURED yet (round-2 candidate): the end-of-ray marker is a valid leaf-flagged reference (offset 0), so the
                              loop needs no sentinel compare per iteration - only triangle-side iterations check for it; costs one extra fetch per ray */
@@ -503,7 +506,14 @@ __device__ __forceinline__ int trace_wide_impl(const AccelView& A, Vec3 o, Vec3 
     const float start_length = (carry && carry->resume) ? carry_start_length : h.t;
     // reciprocal of the normalised direction; zero components -> huge finite (conservative)
     const float big = 1e30f;
+#if RT_TW_RCP_APPROX
+    // round-2 candidate, NOT MEASURED: the reciprocal direction only feeds the conservative node test, whose relative widening (8 ulp)
+    // has room for MUFU.RCP's ~1 ulp - three IEEE divisions (~25 instructions with their slow-path checks) per ray become three MUFUs
+    auto rcp_approx = [](float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; };
+    const float ix = nd.x != 0.0f ? rcp_approx(nd.x) : big, iy = nd.y != 0.0f ? rcp_approx(nd.y) : big, iz = nd.z != 0.0f ? rcp_approx(nd.z) : big;
+#else
     const float ix = nd.x != 0.0f ? 1.0f / nd.x : big, iy = nd.y != 0.0f ? 1.0f / nd.y : big, iz = nd.z != 0.0f ? 1.0f / nd.z : big;
+#endif
     const float kWiden = 1.0e-6f;
     // kFma: abs error of fma(plane, inv, c) is bounded by ~3 ulp of |o * inv|: `slack` covers it, kWiden the relative part
     const float ax = o.x * ix, ay = o.y * iy, az = o.z * iz;

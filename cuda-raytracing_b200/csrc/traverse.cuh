@@ -25,6 +25,9 @@
 #ifndef RT_TW_TRI_PACKED
 #define RT_TW_TRI_PACKED 1   /* tri_test in packed fp32 (FMUL2 / FADD2), bit-identical: 52.9 -> 51.3 ms */
 #endif
+#ifndef RT_TW_BOX_PREFILTER
+#define RT_TW_BOX_PREFILTER 0
+#endif
 #ifndef RT_TW_RCP_APPROX
 #define RT_TW_RCP_APPROX 0
 #endif
@@ -107,6 +110,22 @@ __device__ __forceinline__ bool exact_box(Vec3 o, Vec3 d, const RtBVHNode* node,
 {
     const float4 q0 = ldg4(node);                                    // min.xyz max.x
     const float4 q1 = ldg4(reinterpret_cast<const char*>(node) + 16);  // max.yz first count
+#if RT_TW_BOX_PREFILTER
+    {   // round-2 candidate, NOT MEASURED: the six IEEE divisions below decide almost always far from their thresholds. The same slabs
+        // with MUFU.RCP instead: each quotient fl(s * rcp(d)) is within 2^-22 of the exact test's fl(s / d) (same s = fl(plane - o);
+        // rcp.approx: 2^-23, two roundings: 2^-24 each), and so are the entry / exit distances (a min/max picks another element only
+        // where the two are that close). If the approximate test passes with 1e-6 to spare on every comparison the exact one passes.
+        // Anything else - including every inf / NaN an axis-parallel or denormal component produces - takes the exact path.
+        auto rcp_approx = [](float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; };
+        const float rx = rcp_approx(d.x), ry = rcp_approx(d.y), rz = rcp_approx(d.z);
+        const float ax1 = (q0.x - o.x) * rx, ax2 = (q0.w - o.x) * rx, ay1 = (q0.y - o.y) * ry, ay2 = (q1.x - o.y) * ry;
+        const float az1 = (q0.z - o.z) * rz, az2 = (q1.y - o.z) * rz;
+        const float lo = fmaxf(fmaxf(fminf(ax1, ax2), fminf(ay1, ay2)), fminf(az1, az2));
+        const float hi = fminf(fminf(fmaxf(ax1, ax2), fmaxf(ay1, ay2)), fmaxf(az1, az2));
+        const float lo_up = fmaf(1.0e-6f, fabsf(lo), lo) + 1e-30f, hi_dn = fmaf(-1.0e-6f, fabsf(hi), hi) - 1e-30f;
+        if (hi_dn >= lo_up && lo_up < ray_length && hi_dn > 0.0f) return true;
+    }
+#endif
     const float tx1 = (q0.x - o.x) / d.x, tx2 = (q0.w - o.x) / d.x;
     float tmin = fminf(tx1, tx2), tmax = fmaxf(tx1, tx2);
     const float ty1 = (q0.y - o.y) / d.y, ty2 = (q1.x - o.y) / d.y;

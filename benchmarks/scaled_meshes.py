@@ -6,7 +6,6 @@ For each: primary-ray parity property at 1080p (product traversal == reference-o
 path tracing 1080p / 4 bounces, Mrays/s, and the bytes-per-ray roofline from reference-order work counters.
     python benchmarks/scaled_meshes.py [a|b|ab]"""
 import json
-import math
 import os
 import sys
 import time
@@ -19,42 +18,13 @@ for p in (ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "oracle")):
         sys.path.insert(0, p)
 import util  # noqa: E402
 
-GRID_POSE = ((165.0, 60.0, -40.0), -20.0, 180.0)  # above the 10x10 grid, looking along +z and down: bunnies cover 22 % of the pixels
-
-
-def bunny_transform(tx, ty, tz):
-    """T(tx,ty,tz) * Ry(-pi) * Rx(pi/2) * S(150): the reference's bunny placement (RayTracing.cpp:42-46) moved to (tx,ty,tz)."""
-    c, s = math.cos(-math.pi), math.sin(-math.pi)
-    ry = np.array([[c, 0, s, 0], [0, 1, 0, 0], [-s, 0, c, 0], [0, 0, 0, 1]], np.float32)
-    c2, s2 = math.cos(math.pi / 2), math.sin(math.pi / 2)
-    rx = np.array([[1, 0, 0, 0], [0, c2, -s2, 0], [0, s2, c2, 0], [0, 0, 0, 1]], np.float32)
-    t = np.eye(4, dtype=np.float32); t[:3, 3] = (tx, ty, tz)
-    return t @ ry @ rx @ np.diag([150, 150, 150, 1]).astype(np.float32)
+GRID_POSE = util.GRID_POSE
+bunny_transform = util.bunny_transform
 
 
 def build_scene(rt, which, env=True):
-    a = util.assets()
-    t0 = time.time()
-    scene = rt.Scene(a["dds"] if env else None)
-    scene.setup_cornell_box()
-    if which == "a":
-        mesh = rt.Mesh(a["obj"], subdivide=2)
-        scene.setup_stanford_bunny(mesh)
-        pose = util.POSES["poseB"]
-    else:
-        mesh = rt.Mesh(a["obj"])
-        m = scene.add_material(albedo=(1, 1, 1), specular=(0.3, 1.0, 0.3, 0.0), roughness=0.8, specular_percent=0.5)
-        for gx in range(10):
-            for gz in range(10):
-                scene.add_loaded_scene(mesh, bunny_transform(30 + 30 * gx, -18, 20 + 30 * gz), m)
-        # no floor quad here: with BVH.cpp's midpoint split two grid-sized triangles pin ~3 M primitives into ONE leaf (their boxes
-        # set the node bounds while every other centroid falls on one side, BVH.cpp:79-107) - measured once: 2.15 M reference-order
-        # triangle tests per ray. The fat-leaf sub-tree copes (1.26 Grays/s) but the reference-order counters become meaningless.
-        pose = GRID_POSE
-    t1 = time.time()
-    scene.build_bvh()
-    t2 = time.time()
-    return scene, mesh, pose, {"assemble_s": t1 - t0, "bvh_build_s": t2 - t1}
+    """The config-4 scenes live in tests/util.py (the -m gpu parity tests build the same ones)."""
+    return util.scaled_scene(rt, which, env)
 
 
 def main():

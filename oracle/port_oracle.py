@@ -29,6 +29,7 @@ def lib():
         h.port_rng_sphere.argtypes = [C.c_void_p, C.c_void_p]
         h.port_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_int,
                                   C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        h.port_ambient_occlusion.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = h
     return _lib
 
@@ -64,6 +65,12 @@ class PortScene:
         ids = np.zeros(len(rays), np.uint32); ts = np.zeros(len(rays), np.float32)
         lib().port_trace_rays(_p(self.buf), _p(rays), len(rays), int(with_spheres), tie_mode, _p(ids), _p(ts))
         return ids, ts
+
+    def ambient_occlusion(self, rng_states, width, height, ao_rays=16, tie_mode=0):
+        """BASELINE config 3 on the host: (unoccluded fraction per pixel, primary hit ids, closest-hit queries issued)."""
+        ao = np.zeros(width * height, np.float32); ids = np.zeros(width * height, np.uint32); n = np.zeros(1, np.uint64)
+        lib().port_ambient_occlusion(_p(self.buf), _p(rng_states), width, height, ao_rays, tie_mode, _p(ao), _p(ids), _p(n))
+        return ao, ids, int(n[0])
 
     def render(self, rng_states, surface, last, width, height, frame_index, spp=5, bounces=6, blend_mode=0, tie_mode=0,
                row_begin=0, row_end=0, row_stride=1, counters=None):

@@ -22,6 +22,8 @@
  *   port_render_pixel        RayTracing/main_raytracing.cu:162-200
  *   xorwow_*                 curand_kernel.h:863-874 (curand), :742-790 (curand_init), curand_uniform.h:69-72
  *   port_point_on_sphere     RayTracing/Random.h:23-31
+ *   port_ambient_occlusion   BASELINE.json config 3: primary hit at the pixel centre, then ao_rays rays in the
+ *                            reference's own diffuse lobe normalize(n + S) from p + 0.01 n (main_raytracing.cu:129,135)
  */
 #include <float.h>
 #include <math.h>
@@ -465,6 +467,45 @@ PORT_API void port_rng_init_many(PRng* states, uint64_t count, uint64_t seed, ui
 PORT_API void port_rng_draw(PRng* s, uint32_t n, uint32_t* out) { for (uint32_t i = 0; i < n; i++) out[i] = port_curand(s); }
 PORT_API void port_rng_uniform(PRng* s, uint32_t n, float* out) { for (uint32_t i = 0; i < n; i++) out[i] = port_uniform(s); }
 PORT_API void port_rng_sphere(PRng* s, float* out3) { const v3 p = port_point_on_sphere(s); out3[0] = p.x; out3[1] = p.y; out3[2] = p.z; }
+
+/*
+ * BASELINE.json config 3, the incoherent-ray stress: per pixel one pixel-centre primary ray through GetRayHit
+ * (main_raytracing.cu:83-109); on a hit, `ao_rays` closest-hit queries along normalize(hit.normal + GetRandomPointOnSphere())
+ * (the diffuse lobe of main_raytracing.cu:129, two draws per ray, Random.h:23-31) from hit.position + hit.normal * 0.01
+ * (:135). out_ao = unoccluded / ao_rays (1 where the primary ray misses: no draws); out_id (optional) = primary hit id.
+ * The reference has no AO kernel: this is its lobe, offset, RNG stream and closest-hit query in the sequence
+ * csrc/pathtrace.cu ambient_occlusion_kernel issues them.
+ */
+PORT_API void port_ambient_occlusion(const PScene* s, PRng* rng_states, int width, int height, int ao_rays, int tie_mode,
+                                     float* out_ao, uint32_t* out_id, uint64_t* ray_count)
+{
+    uint64_t c_rays = 0;
+#pragma omp parallel for schedule(dynamic, 2) reduction(+ : c_rays)
+    for (int y = 0; y < height; y++)
+        for (int x = 0; x < width; x++)
+        {
+            const size_t i = (size_t)y * width + x;
+            PRng* rng = &rng_states[i];
+            const float u = ((float)x + 0.5f) / (float)width, v = ((float)y + 0.5f) / (float)height;
+            v3 o, d; port_camera_ray(&s->camera, u, v, &o, &d);
+            PHit h;
+            c_rays++;
+            const int hit = port_get_ray_hit(s, o, d, &h, 1, tie_mode, NULL);
+            if (out_id) out_id[i] = h.id;
+            if (!hit) { out_ao[i] = 1.0f; continue; }
+            const v3 base = add(h.position, scale(h.normal, 0.01f));
+            int unoccluded = 0;
+            for (int k = 0; k < ao_rays; k++)
+            {
+                const v3 dir = normalize(add(h.normal, port_point_on_sphere(rng)));
+                PHit h2;
+                c_rays++;
+                if (!port_get_ray_hit(s, base, dir, &h2, 1, tie_mode, NULL)) unoccluded++;
+            }
+            out_ao[i] = ao_rays ? (float)unoccluded / (float)ao_rays : 1.0f;
+        }
+    if (ray_count) *ray_count += c_rays;
+}
 
 /*
  * raytracing_kernel_main (main_raytracing.cu:162-200) for rows [row_begin, row_end) stepping row_stride.

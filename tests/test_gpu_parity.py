@@ -217,18 +217,25 @@ def test_path_trace_frames_vs_reference_golden(rt, torch_cuda):
     body pixel by pixel. Residual differences: device sinf/cosf vs glibc, hardware cubemap filter vs cubemap_cpu.h."""
     g = golden("pt_96x72.npz")
     d = gpu_util.DeviceScene(rt, torch_cuda, 96, 72, "poseB", seed=1234, env=True)
+    measured = []
     for f in range(3):
         d.process(f, write_last=1)
         got = d.surface.cpu().numpy()
         want = g["frames"][f]
         assert (got[..., 3] == 1).all()
         close = np.isclose(got[..., :3], want[..., :3], rtol=2e-2, atol=2e-3).all(axis=-1)
-        assert close.mean() > 0.97, (f, close.mean())
-        assert rel_rmse(got, want) < 0.05, (f, rel_rmse(got, want))
+        measured.append((f, float(close.mean()), rel_rmse(got, want)))
+        # frame 0 measured 0.994 / 0.6 %; a pixel whose path length differs once (device sinf/cosf vs libm at a grazing hit) has
+        # another RNG stream from then on, so the per-pixel agreement of the running mean decays a little with every frame
         assert np.array_equal(d.last.cpu().numpy(), got)  # folded D2D copy (RayTracing.cpp:233)
     # the per-pixel XORWOW streams advanced by the same number of draws as the reference's (path lengths equal)
     st = d.rng.cpu().numpy().reshape(-1, 48)[: 96 * 72, :24]
     same = (st == g["rng_v"]).all(axis=1).mean()
+    os.makedirs(os.path.join(util.ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(util.ROOT, "gpurun_out", "golden_frames_measured.txt"), "w") as fh:
+        fh.write("frame, pixels within 2e-2, rel RMSE: %s; identical RNG streams after 3 frames: %.4f\n" % (measured, same))
+    for f, c, r in measured:
+        assert c > 0.99 - 0.01 * f and r < 0.02, measured
     assert same > 0.97, same
 
 
@@ -424,9 +431,10 @@ def test_against_reference_cuda_kernel_on_device(rt, torch_cuda, ref):
     with open(os.path.join(util.ROOT, "gpurun_out", "vs_reference_cuda_kernel.txt"), "w") as f:
         f.write(f"pixels within 2e-2: {close:.4f}  8x8-block rel RMSE: {block_rmse:.4f}  mean ratio: {mean_ratio:.4f}  "
                 f"identical RNG streams after {frames} frames: {same_stream:.4f}\n")
-    assert close > 0.6, close
-    assert block_rmse < 0.2, block_rmse
-    assert abs(mean_ratio - 1) < 0.03, mean_ratio
+    # bars = 3x the measured values (0.73 / 0.0147 / 1.002, profiles/r01a_vs_reference_cuda_kernel.txt)
+    assert close > 0.70, close
+    assert block_rmse < 0.045, block_rmse
+    assert abs(mean_ratio - 1) < 0.01, mean_ratio
 
 
 @pytest.mark.parametrize("size", [(64, 48), (37, 23), (200, 120)])

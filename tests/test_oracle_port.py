@@ -130,3 +130,30 @@ def test_port_sum_mode_and_counters(port, bunny, pscene):
     before = acc.copy()
     pscene.render(st, acc, None, W, H, 0, spp=3, bounces=4, blend_mode=1, row_begin=10, row_end=10)
     assert np.array_equal(before, acc)
+
+
+def test_ao_port_sequence_and_stream(rt, bunny):
+    """oracle/rt_port.c port_ambient_occlusion (BASELINE config 3) is a composition of pinned pieces (GetRayHit, the diffuse lobe,
+    XORWOW): check what is its own - one primary query per pixel, 16 more per hit, two draws per AO ray and none on a miss
+    (final states = the states 32 draws further), counts in sixteenths."""
+    import port_oracle as po
+    W, H, N = 64, 48, 16
+    a = bunny["arrays"]
+    scene = bunny["scene"]
+    scene.set_camera(*util.POSES["poseB"], W, H)
+    cam, _ = scene.camera()
+    ps = po.PortScene({k: util.raw(a[k]) for k in ("vertices", "faces", "spheres", "materials")}, util.raw(a["nodes"]), a["face_indices"],
+                      cam.view(np.uint8).ravel().copy())
+    st = po.rng_init(W * H, 5)
+    before = st.copy()
+    ao, ids, rays = ps.ambient_occlusion(st, W, H, N, 0)
+    pid, _ = ps.primary_hits(W, H, 1, 0)
+    assert np.array_equal(ids, pid)
+    hit = ids != 0xFFFFFFFF
+    assert rays == W * H + N * int(hit.sum()) and 0.3 < hit.mean() < 1.0
+    assert (ao[~hit] == 1).all() and np.array_equal((ao * N).round() / N, ao) and 0.05 < ao[hit].mean() < 0.99
+    for i in (0, 7, int(np.flatnonzero(hit)[0]), int(np.flatnonzero(hit)[-1])):
+        s = before[i].copy()
+        if hit[i]:
+            po.rng_draw(s, 2 * N)
+        assert np.array_equal(s[:24], st[i, :24])

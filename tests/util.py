@@ -66,6 +66,49 @@ def bunny_scene(rt, env=False):
     return scene, mesh
 
 
+# ---- BASELINE config 4: synthetic scaled meshes ----------------------------------------------------------
+GRID_POSE = ((165.0, 60.0, -40.0), -20.0, 180.0)  # above the 10x10 grid, looking along +z and down: bunnies cover 22 % of the pixels
+
+
+def bunny_transform(tx, ty, tz):
+    """T(tx,ty,tz) * Ry(-pi) * Rx(pi/2) * S(150): the reference's bunny placement (RayTracing.cpp:42-46) moved to (tx,ty,tz)."""
+    import math
+    c, s = math.cos(-math.pi), math.sin(-math.pi)
+    ry = np.array([[c, 0, s, 0], [0, 1, 0, 0], [-s, 0, c, 0], [0, 0, 0, 1]], np.float32)
+    c2, s2 = math.cos(math.pi / 2), math.sin(math.pi / 2)
+    rx = np.array([[1, 0, 0, 0], [0, c2, -s2, 0], [0, s2, c2, 0], [0, 0, 0, 1]], np.float32)
+    t = np.eye(4, dtype=np.float32); t[:3, 3] = (tx, ty, tz)
+    return t @ ry @ rx @ np.diag([150, 150, 150, 1]).astype(np.float32)
+
+
+def scaled_scene(rt, which, env=True, grid=10):
+    """BASELINE config 4 scenes through the reference's own AddLoadedScene semantics (every face twice, Scene.cpp:75-132):
+    'a' = 2x Loop-subdivided bunny in the reference scene (2 222 432 BVH triangles, one 1 079-prim reference leaf);
+    'b' = grid x grid bunnies, pitch 30 in x/z, in the Cornell box scene WITHOUT the floor quad (10x10: 13 890 200 triangles;
+    with BVH.cpp's midpoint split two grid-sized floor triangles pin ~3 M primitives into one leaf, BVH.cpp:79-107).
+    Returns (scene, mesh, pose, timings)."""
+    import time
+    a = assets()
+    t0 = time.time()
+    scene = rt.Scene(a["dds"] if env else None)
+    scene.setup_cornell_box()
+    if which == "a":
+        mesh = rt.Mesh(a["obj"], subdivide=2)
+        scene.setup_stanford_bunny(mesh)
+        pose = POSES["poseB"]
+    else:
+        mesh = rt.Mesh(a["obj"])
+        m = scene.add_material(albedo=(1, 1, 1), specular=(0.3, 1.0, 0.3, 0.0), roughness=0.8, specular_percent=0.5)
+        for gx in range(grid):
+            for gz in range(grid):
+                scene.add_loaded_scene(mesh, bunny_transform(30 + 30 * gx, -18, 20 + 30 * gz), m)
+        pose = GRID_POSE
+    t1 = time.time()
+    scene.build_bvh()
+    t2 = time.time()
+    return scene, mesh, pose, {"assemble_s": t1 - t0, "bvh_build_s": t2 - t1}
+
+
 def raw(a):
     """uint8 [n, itemsize] view of a structured array (what oracle/ref_oracle.py takes)."""
     return np.ascontiguousarray(a).view(np.uint8).reshape(len(a), -1)

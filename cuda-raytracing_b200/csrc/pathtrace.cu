@@ -359,7 +359,7 @@ __global__ void __launch_bounds__(256) ambient_occlusion_kernel(AccelView A, Sce
                 base = position + normal * 0.01f;
             }
             else { total++; if (h.id == RT_MISS_ID) unoccluded++; }
-            o = base; d = normalize3(normal + rng.point_on_sphere());
+            if (k < ao_rays) { o = base; d = normalize3(normal + rng.point_on_sphere()); }  // two draws per AO ray, none after the last
         }
         rng.store(state);
         out[(size_t)y * width + x] = total ? (float)unoccluded / (float)total : 1.0f;

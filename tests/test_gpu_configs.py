@@ -151,7 +151,7 @@ def test_config4_scaled_meshes_vs_port(rt, torch_cuda, which):
     assert np.array_equal(low_t.view(np.uint32), ref_t.view(np.uint32))
     ids, ts = d.trace_rays(rays, True, 0)
     check_ids(ids, ts, low_id, ref_t, first_id)
-    assert (ids != 0xFFFFFFFF).mean() > 0.5
+    assert (ids != 0xFFFFFFFF).mean() > (0.5 if which == "a" else 0.15)  # b: no floor, open sky between the bunnies
     pf_id, pf_t = ps.primary_hits(W, H, 1, 0)
     pl_id, _ = ps.primary_hits(W, H, 1, 1)
     pid, pts = d.trace_primary(1, 0)

@@ -24,4 +24,4 @@ print(json.dumps({"rays": len(rays), "hit": int((i0 != 0xFFFFFFFF).sum()), "t_di
                   "product_closer": int((t0 < t1).sum()), "reference_order_closer": int((t1 < t0).sum()),
                   "same_t_other_id": int(((ulp == 0) & (i0 != i1)).sum()), "max_ulp": int(ulp.max()),
                   "max_rel": float((np.abs(t0 - t1) / np.maximum(t1, 1e-30)).max()),
-                  "accel": {k: int(v) for k, v in dev.scene.accel_info().items()}}))  # twin_pairs > 0 only in an RT_TW_TWIN=1 build
+                  "accel": {k: int(v) for k, v in dev.scene.accel_info().items()}}))

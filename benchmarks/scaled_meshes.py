@@ -85,7 +85,7 @@ def main():
         import ctypes as C
         inf = (C.c_uint64 * 8)()
         rt.check(rt.lib().rt_accel_info(d.accel, inf))
-        info["accel_device_bytes"] = int(inf[5] | (inf[6] << 32)); info["wide_nodes"] = int(inf[0]); info["fat_leaves"] = int(inf[3] & 0xFFFFFFFF); info["twin_pairs"] = int(inf[3] >> 32)
+        info["accel_device_bytes"] = int(inf[5] | (inf[6] << 32)); info["wide_nodes"] = int(inf[0]); info["fat_leaves"] = int(inf[3])
         print(json.dumps(info), flush=True)
         del d, scene, mesh
         torch.cuda.empty_cache()

@@ -132,7 +132,7 @@ class Scene:
 def _accel_info(handle):
     v = (C.c_uint64 * 8)()
     check(lib().rt_accel_info(handle, v))
-    return {"wide_nodes": v[0], "slots": v[1], "ref_leaves": v[2], "fat_leaves": v[3] & 0xFFFFFFFF, "twin_pairs": v[3] >> 32,
+    return {"wide_nodes": v[0], "slots": v[1], "ref_leaves": v[2], "fat_leaves": v[3],
             "wide_depth": v[4], "device_bytes": v[5] | (v[6] << 32), "ref_depth": v[7]}
 
 

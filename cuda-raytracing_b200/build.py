@@ -93,6 +93,17 @@ def build(force=False, verbose=False, defines=(), out=None):
     return target
 
 
+REDO_LIB = os.path.join(LIB_DIR, "libb200rt_redo.so")
+
+
+def build_redo_variant(force=False):
+    """Test build (tests/test_gpu_redo_build.py): RT_TW_FORCE_REDO=7 sends every ray whose winning slot is a multiple of 8 through
+    the redo path of trace_wide (per-candidate exact leaf-box check), which a grazing ray takes about never."""
+    if not force and os.path.exists(REDO_LIB) and os.path.getmtime(REDO_LIB) >= _newest_source_mtime():
+        return REDO_LIB
+    return build(defines=["RT_TW_FORCE_REDO=7"], out="libb200rt_redo.so")
+
+
 if __name__ == "__main__":
     defs = [a[2:] for a in sys.argv[1:] if a.startswith("-D")]
     outs = [a[6:] for a in sys.argv[1:] if a.startswith("--out=")]

@@ -32,60 +32,30 @@
 #define RT_REF_BYTE_MASK 0x7FFFFFF0u
 #define RT_REF_COUNT_MASK 0x0000000Fu
 #define RT_MAX_LEAF_PRIMS 16u
-// TriRecord::ref_leaf bit 31: the NEXT slot of the same leaf holds this face's duplicate (same v0, e1/e2 exchanged - the flat copy
-// Scene::AddLoadedScene appends to every smooth face, Scene.cpp:110-127); traverse.cuh skips it after a proven-margin miss.
-#ifndef RT_TW_TWIN
-#define RT_TW_TWIN 0   /* build switch shared by accel_build.cpp (pair + flag the copies) and traverse.cuh (skip them): measured slower, off */
-#endif
-// Wide-node boxes as centre + half extent (build switch shared by accel_build.cpp and the traversal kernels): the entry / exit
-// distance per axis is mid -/+ half * |1/d| with mid = (centre - o) / d, all on the fma pipe - no min/max per axis (ALU pipe).
-// Half extents are rounded up and inflated by 2^-21 (+ the centre's own rounding) at build time, so the stored box is a superset.
-#ifndef RT_TW_CENTER
-#define RT_TW_CENTER 1   /* 49.8 -> 46.0 ms, frame + RNG bit-identical (the ALU pipe, not the issue port, bounds the node step) */
-#endif
-#define RT_TWIN_BIT 0x80000000u
+// Wide-node boxes are stored as centre + half extent: the entry / exit distance per axis is mid -/+ half * |1/d| with
+// mid = (centre - o) / d, all on the fma pipe - no min/max per axis on the ALU pipe (49.8 -> 46.0 ms against the lo/hi form, bit-identical
+// results). Half extents are rounded up and inflated by 2^-21 (+ the centre's own rounding) at build time, so the stored box is a
+// superset; exactness is the reference-leaf check's business (traverse.cuh).
 #define RT_REF_LEAF_MASK 0x7FFFFFFFu
 #define RT_STACK_SIZE 64
 
 struct RtFloat4 { float x, y, z, w; };
 
-// 48-byte wide node (RT_TW_NODE48, needs RT_TW_CENTER; round-2 candidate, NOT MEASURED): the same three 128-bit loads as a triangle
-// record and no fourth. Centres stay fp32, the six half extents are bf16 ROUNDED UP, two per word; the kernel uses the high one as the
-// word stands (the other value's bits in its low mantissa only enlarge it) and the low one as word << 16 (fma pipe).
-#ifndef RT_TW_NODE48
-#define RT_TW_NODE48 0
-#endif
-#if RT_TW_NODE48 && !RT_TW_CENTER
-#error "RT_TW_NODE48 stores centre + half extent boxes"
-#endif
-#if RT_TW_NODE48
-struct alignas(16) WideNode
-{
-    RtFloat4 a;          // centre0.x centre0.y | centre1.x centre1.y
-    float cz[2];         // centre0.z centre1.z
-    uint32_t hxy[2];     // per child: bf16(half.x) | bf16(half.y) << 16
-    uint32_t hz;         // bf16(half0.z) | bf16(half1.z) << 16
-    uint32_t child[2];
-    uint32_t pad;
-};
-static_assert(sizeof(WideNode) == 48, "WideNode layout");
-#else
 struct alignas(64) WideNode
 {
     // register-pair friendly order for Blackwell's packed fp32 ops (add/mul/fma .f32x2): every aligned pair of a 128-bit load
     // is combined with one per-ray constant pair, (x, y) or (z, z)
-    RtFloat4 a;   // lo0.x lo0.y | hi0.x hi0.y      (RT_TW_CENTER: centre0.x centre0.y | half0.x half0.y)
-    RtFloat4 b;   // lo1.x lo1.y | hi1.x hi1.y      (RT_TW_CENTER: centre1.x centre1.y | half1.x half1.y)
-    RtFloat4 c;   // lo0.z hi0.z | lo1.z hi1.z      (RT_TW_CENTER: centre0.z centre1.z | half0.z half1.z)
+    RtFloat4 a;   // centre0.x centre0.y | half0.x half0.y
+    RtFloat4 b;   // centre1.x centre1.y | half1.x half1.y
+    RtFloat4 c;   // centre0.z centre1.z | half0.z half1.z
     uint32_t child[2];
     uint32_t pad[2];
 };
-#endif
 
 struct alignas(16) TriRecord
 {
     float v0[3]; uint32_t face_id;
-    float e1[3]; uint32_t ref_leaf;   // index of the reference leaf node (for the exact box re-check) | RT_TWIN_BIT
+    float e1[3]; uint32_t ref_leaf;   // index of the reference leaf node (for the exact box re-check)
     float e2[3]; uint32_t orig_slot; // slot before any fat-leaf permutation (reference visiting order)
 };
 
@@ -104,7 +74,7 @@ struct AccelHost
     std::vector<ShadeRecord> shade;    // one per BVH slot
     uint32_t root_ref = RT_SENTINEL;
     uint32_t tri_byte0 = 0;            // byte offset of tris[0] in the arena = 64 * wide.size()
-    uint32_t ref_leaf_count = 0, fat_leaf_count = 0, wide_depth = 0, ref_depth = 0, twin_pair_count = 0;
+    uint32_t ref_leaf_count = 0, fat_leaf_count = 0, wide_depth = 0, ref_depth = 0;
 };
 
 // Returns 0, or a negative RT_E_* (include/b200rt.h).
@@ -132,5 +102,5 @@ struct RtAccel
 {
     AccelView view{};
     uint64_t device_bytes = 0;
-    uint32_t wide_count = 0, slot_count = 0, ref_leaf_count = 0, fat_leaf_count = 0, wide_depth = 0, ref_depth = 0, twin_pair_count = 0;
+    uint32_t wide_count = 0, slot_count = 0, ref_leaf_count = 0, fat_leaf_count = 0, wide_depth = 0, ref_depth = 0;
 };

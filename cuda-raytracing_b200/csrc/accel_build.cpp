@@ -37,26 +37,16 @@ namespace
 
     inline uint32_t LeafRef(uint32_t first, uint32_t count) { return RT_LEAF_BIT | ((count - 1u) << 27) | first; }
 
-#if RT_TW_CENTER
     // centre and half extent of child `which` exactly as the kernels read them (traverse.cuh center_slabs)
     inline void ChildCentreHalf(const WideNode& w, int which, float ctr[3], float half[3])
     {
-#if RT_TW_NODE48
-        auto as_float = [](uint32_t bits) { float v; std::memcpy(&v, &bits, 4); return v; };
-        ctr[0] = which == 0 ? w.a.x : w.a.z; ctr[1] = which == 0 ? w.a.y : w.a.w; ctr[2] = w.cz[which];
-        half[0] = as_float(w.hxy[which] << 16); half[1] = as_float(w.hxy[which]);   // the high value keeps the low one's bits in its mantissa
-        half[2] = which == 0 ? as_float(w.hz << 16) : as_float(w.hz);
-#else
         const RtFloat4& q = which == 0 ? w.a : w.b;
         ctr[0] = q.x; ctr[1] = q.y; ctr[2] = which == 0 ? w.c.x : w.c.y;
         half[0] = q.z; half[1] = q.w; half[2] = which == 0 ? w.c.z : w.c.w;
-#endif
     }
-#endif
 
     inline void SetChildBox(WideNode& w, int which, const Box& b)
     {
-#if RT_TW_CENTER
         float c[3], h[3];
         for (int k = 0; k < 3; k++)
         {   // [c - h, c + h] in exact arithmetic holds [lo, hi]; h carries the 2^-21 the kernel's rounding of h * |1/d| needs
@@ -68,25 +58,8 @@ namespace
             if ((double)hf < need) hf = std::nextafter(hf, INFINITY);
             h[k] = hf;
         }
-#if RT_TW_NODE48
-        auto bf16_up = [](float v) -> uint32_t
-        {   // smallest bf16 >= v for positive finite v; the empty-box marker (negative) is truncated (still hugely negative)
-            uint32_t bits; std::memcpy(&bits, &v, 4);
-            if (!(bits & 0x80000000u) && (bits & 0xFFFFu) && (bits >> 23) != 0xFFu) bits += 0x10000u;
-            return bits >> 16;
-        };
-        if (which == 0) { w.a.x = c[0]; w.a.y = c[1]; } else { w.a.z = c[0]; w.a.w = c[1]; }
-        w.cz[which] = c[2];
-        w.hxy[which] = bf16_up(h[0]) | (bf16_up(h[1]) << 16);
-        w.hz = which == 0 ? ((w.hz & 0xFFFF0000u) | bf16_up(h[2])) : ((w.hz & 0x0000FFFFu) | (bf16_up(h[2]) << 16));
-#else
         if (which == 0) { w.a = { c[0], c[1], h[0], h[1] }; w.c.x = c[2]; w.c.z = h[2]; }
         else { w.b = { c[0], c[1], h[0], h[1] }; w.c.y = c[2]; w.c.w = h[2]; }
-#endif
-#else
-        if (which == 0) { w.a = { b.lo[0], b.lo[1], b.hi[0], b.hi[1] }; w.c.x = b.lo[2]; w.c.y = b.hi[2]; }
-        else { w.b = { b.lo[0], b.lo[1], b.hi[0], b.hi[1] }; w.c.z = b.lo[2]; w.c.w = b.hi[2]; }
-#endif
     }
 
     struct Builder
@@ -96,7 +69,6 @@ namespace
         std::vector<Box> slot_box;      // per slot, for sub-trees
         std::vector<float> slot_centroid;
         int error = 0;
-        bool pair_twins = true;
 
         Box SlotBox(uint32_t s) const
         {
@@ -109,39 +81,13 @@ namespace
             return b;
         }
 
-        // Inside one product leaf [first, first+count): move every face next to its duplicate (bit-equal v0, e1/e2 exchanged:
-        // what Scene::AddLoadedScene's smooth face + AddTriangle flat copy produce, Scene.cpp:110-127) and flag the first of the
-        // pair (RT_TWIN_BIT). Slot order inside a leaf is free: the hit rule is order-independent and exact ties are resolved by
-        // orig_slot / face id, which travel with the record.
-        static bool IsTwin(const TriRecord& a, const TriRecord& b)
-        {
-            return std::memcmp(a.v0, b.v0, 12) == 0 && std::memcmp(a.e1, b.e2, 12) == 0 && std::memcmp(a.e2, b.e1, 12) == 0;
-        }
-        uint32_t LeafWithTwins(uint32_t first, uint32_t count)
-        {
-            if (pair_twins)
-                for (uint32_t i = first; i + 1 < first + count; i++)
-                {
-                    for (uint32_t j = i + 1; j < first + count; j++)
-                        if (IsTwin(out.tris[i], out.tris[j]))
-                        {
-                            std::swap(out.tris[i + 1], out.tris[j]); std::swap(out.shade[i + 1], out.shade[j]);
-                            out.tris[i].ref_leaf |= RT_TWIN_BIT;
-                            out.twin_pair_count++;
-                            i++;  // the copy itself starts no pair
-                            break;
-                        }
-                }
-            return LeafRef(first, count);
-        }
-
         // SAH sweep sub-tree over slots [first, first+count); permutes tris/shade inside the range.
         uint32_t BuildSub(uint32_t first, uint32_t count, uint32_t depth, Box& bounds_out)
         {
             Box bounds = EmptyBox();
             for (uint32_t s = first; s < first + count; s++) Grow(bounds, SlotBox(s));
             bounds_out = bounds;
-            if (count <= 4) return LeafWithTwins(first, count);
+            if (count <= 4) return LeafRef(first, count);
 
             std::vector<uint32_t> order(count);
             std::vector<Box> boxes(count);
@@ -200,7 +146,7 @@ namespace
                 out.ref_leaf_count++;
                 if ((uint64_t)node.first_index + node.prim_count > out.tris.size()) { error = RT_E_INVALID; return RT_SENTINEL; }
                 for (uint32_t s = node.first_index; s < node.first_index + node.prim_count; s++) out.tris[s].ref_leaf = n;
-                if (node.prim_count <= threshold) return LeafWithTwins(node.first_index, node.prim_count);
+                if (node.prim_count <= threshold) return LeafRef(node.first_index, node.prim_count);
                 out.fat_leaf_count++;
                 Box unused;
                 return BuildSub(node.first_index, node.prim_count, depth, unused);
@@ -256,7 +202,7 @@ int BuildAccelHost(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* 
     }
     if (invalid) return RT_E_INVALID;
     lap("gather records");
-    Builder builder{ nodes, node_count, fat_leaf_threshold, out, {}, {}, 0, RT_TW_TWIN != 0 && std::getenv("B200RT_NO_TWINS") == nullptr };
+    Builder builder{ nodes, node_count, fat_leaf_threshold, out, {}, {}, 0 };
     out.wide.reserve(node_count / 2 + 16);
     out.root_ref = builder.Emit(0, 0);
     lap("wide nodes");
@@ -312,7 +258,6 @@ int CheckAccelHost(const AccelHost& a, const RtBVHNode* nodes, uint32_t node_cou
                 if (rl >= node_count || nodes[rl].prim_count == 0) return fail("ref_leaf is not a reference leaf");
                 if (t.orig_slot < nodes[rl].first_index || t.orig_slot >= nodes[rl].first_index + nodes[rl].prim_count) return fail("orig_slot outside its reference leaf");
                 if (rl != leaf_node && nodes[rl].prim_count <= RT_MAX_LEAF_PRIMS && nodes[leaf_node].prim_count <= RT_MAX_LEAF_PRIMS) return fail("product leaf mixes reference leaves");
-                if ((t.ref_leaf & RT_TWIN_BIT) && s + 1 >= first + count) return fail("twin flag on the last record of a leaf");
             }
             leaves++;
         }
@@ -327,7 +272,7 @@ int CheckAccelHost(const AccelHost& a, const RtBVHNode* nodes, uint32_t node_cou
     }
     for (uint8_t v : seen) if (v != 1) return fail("slot not reachable from the root");
     if (arena + 64 > RT_REF_BYTE_MASK) return fail("arena larger than the reference range");
-    // Box containment, bottom-up: the stored box of every wide-node child (lo/hi planes, or centre + half extent: RT_TW_CENTER) must
+    // Box containment, bottom-up: the stored box of every wide-node child (centre + half extent) must
     // hold, in exact arithmetic, the reference leaf boxes of everything below it (a fat leaf's private sub-tree: the triangles below).
     // This is what makes the conservative node test safe to cull with; exactness is the deferred reference-leaf check's business.
     struct DBox { double lo[3], hi[3]; };
@@ -365,14 +310,9 @@ int CheckAccelHost(const AccelHost& a, const RtBVHNode* nodes, uint32_t node_cou
         {
             const DBox cb = self(self, w.child[c]);
             double lo[3], hi[3];
-#if RT_TW_CENTER
             float ctr[3], half[3];
             ChildCentreHalf(w, c, ctr, half);
             for (int k = 0; k < 3; k++) { lo[k] = (double)ctr[k] - (double)half[k]; hi[k] = (double)ctr[k] + (double)half[k]; }
-#else
-            const RtFloat4& q = c == 0 ? w.a : w.b;
-            lo[0] = q.x; lo[1] = q.y; hi[0] = q.z; hi[1] = q.w; lo[2] = c == 0 ? w.c.x : w.c.z; hi[2] = c == 0 ? w.c.y : w.c.w;
-#endif
             for (int k = 0; k < 3; k++) if (!(lo[k] <= cb.lo[k] && hi[k] >= cb.hi[k])) contained = false;
             grow(cb.lo, cb.hi);
         }
@@ -380,7 +320,6 @@ int CheckAccelHost(const AccelHost& a, const RtBVHNode* nodes, uint32_t node_cou
     };
     bounds(bounds, a.root_ref);
     if (!contained) return fail("a wide-node child box does not contain the reference boxes below it");
-#if RT_TW_CENTER
     // The node test itself, replayed on the host in the kernel's own fp32 arithmetic (traverse.cuh center_slabs + the relative widening:
     // float subtract, float multiply, fmaf - this file is compiled with -ffp-contract=off): rays that hit what lies below a child, by an
     // exact double-precision slab test of the contained bounds, must pass it. Deterministic sample of children, rays from near, far, and
@@ -444,7 +383,6 @@ int CheckAccelHost(const AccelHost& a, const RtBVHNode* nodes, uint32_t node_cou
             }
         }
     }
-#endif
     if (info4) { info4[0] = inner; info4[1] = leaves; info4[2] = max_depth; info4[3] = arena; }
     return 0;
 }

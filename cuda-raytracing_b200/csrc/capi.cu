@@ -113,7 +113,7 @@ int rt_accel_create(const RtBVHNode* nodes, uint32_t node_count, const uint32_t*
     a->device_bytes = bw + bt + bs + br;
     a->wide_count = (uint32_t)host.wide.size(); a->slot_count = (uint32_t)host.tris.size();
     a->ref_leaf_count = host.ref_leaf_count; a->fat_leaf_count = host.fat_leaf_count;
-    a->wide_depth = host.wide_depth; a->ref_depth = host.ref_depth; a->twin_pair_count = host.twin_pair_count;
+    a->wide_depth = host.wide_depth; a->ref_depth = host.ref_depth;
     *out = a;
     return RT_OK;
 }
@@ -145,7 +145,7 @@ int rt_accel_destroy(RtAccel* a)
 int rt_accel_info(const RtAccel* a, uint64_t* info8)
 {
     if (!a || !info8) return Fail(RT_E_INVALID, "rt_accel_info: null");
-    info8[0] = a->wide_count; info8[1] = a->slot_count; info8[2] = a->ref_leaf_count; info8[3] = (uint64_t)a->fat_leaf_count | ((uint64_t)a->twin_pair_count << 32);
+    info8[0] = a->wide_count; info8[1] = a->slot_count; info8[2] = a->ref_leaf_count; info8[3] = a->fat_leaf_count;
     info8[4] = a->wide_depth; info8[5] = a->device_bytes & 0xFFFFFFFFull; info8[6] = a->device_bytes >> 32; info8[7] = a->ref_depth;
     return RT_OK;
 }

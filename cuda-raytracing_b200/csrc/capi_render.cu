@@ -282,14 +282,7 @@ int rt_trace_rays(const RtAccel* accel, const RtGPUScene* scene, const float* d_
                   int with_spheres, int variant, uint32_t* d_id, float* d_t, unsigned long long* d_ray_counter, void* stream)
 {
     if (!accel || !scene || (ray_count && (!d_rays || !d_id || !d_t))) return Fail(RT_E_INVALID, "rt_trace_rays: bad argument");
-    if (variant < 0 || variant > 2) return Fail(RT_E_INVALID, "rt_trace_rays: unknown variant");
-    if (variant == 2)
-    {
-        unsigned int* counter = nullptr;
-        if (int r = NextCounter(&counter)) return r;
-        RT_CUDA(LaunchExtendRays(accel->view, MakeSceneView(scene), d_rays, ray_count, with_spheres != 0, d_id, d_t, d_ray_counter, counter, (cudaStream_t)stream));
-        return RT_OK;
-    }
+    if (variant < 0 || variant > 1) return Fail(RT_E_INVALID, "rt_trace_rays: unknown variant");
     RT_CUDA(LaunchTraceRays(accel->view, MakeSceneView(scene), d_rays, ray_count, with_spheres != 0, variant, d_id, d_t, d_ray_counter, (cudaStream_t)stream));
     return RT_OK;
 }
@@ -315,7 +308,8 @@ int rt_process_ex(const RtProcessParams* p)
     if (p->samples_per_launch <= 0 || p->max_bounces <= 0) return Fail(RT_E_INVALID, "rt_process_ex: spp and bounces must be positive");
     if (p->pitch < (uint64_t)p->width * 16) return Fail(RT_E_INVALID, "rt_process_ex: pitch smaller than a row");
     if (!p->scene->rng_state) return Fail(RT_E_INVALID, "rt_process_ex: scene has no rng_state");
-    if (p->variant < 0 || p->variant > 2) return Fail(RT_E_INVALID, "rt_process_ex: unknown variant");
+    if (p->variant < 0 || p->variant > 3) return Fail(RT_E_INVALID, "rt_process_ex: unknown variant");
+    if (p->write_last_frame && !p->surface_last_frame) return Fail(RT_E_INVALID, "rt_process_ex: write_last_frame needs surface_last_frame");
     if (p->variant == 1)
     {
         unsigned int* counter = nullptr;

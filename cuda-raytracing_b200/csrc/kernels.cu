@@ -202,209 +202,3 @@ cudaError_t LaunchTonemap(const void* surface, int width, int height, uint64_t p
     tonemap_kernel<<<grid, block, 0, stream>>>((const unsigned char*)surface, width, height, pitch, 1.0f / divide_by, d_rgba8);
     return cudaGetLastError();
 }
-
-// ------------------------------------------------------------------------------------------------
-// Persistent "extend" kernel (variant 2 of rt_trace_rays; the traversal stage of the wavefront path tracer):
-// warps stay resident and pull rays from a global counter; a lane whose ray ended is refilled as soon as kFetch lanes are
-// idle; traversal is warp-synchronous in two voted phases - one wide node per lane (leaves are postponed, up to three per
-// lane), and one postponed leaf per lane when enough lanes hold one - so neither phase waits for the longest lane.
-// Same arithmetic and hit rule as trace_wide (results identical; tests compare the variants bit for bit).
-// ------------------------------------------------------------------------------------------------
-struct ExtendLane
-{
-    Vec3 o, d, nd;
-    float ix, iy, iz, cx, cy, cz, slack, start_length;
-    HitRecord h;
-    uint32_t node, pend0, pend1, pend2, verified_leaf;
-    int npend, sp;
-};
-
-template <bool kTieById>
-__device__ __forceinline__ void extend_leaf(const AccelView& A, uint32_t leaf, ExtendLane& L)
-{
-    const uint32_t first = ref_slot(A, leaf), count = ref_count(leaf);
-    const TriRecord* tr = A.tris + first;
-    for (uint32_t i = 0; i < count; i++)
-    {
-        const float4 r0 = ldg4(&tr[i]), r1 = ldg4(reinterpret_cast<const char*>(&tr[i]) + 16), r2 = ldg4(reinterpret_cast<const char*>(&tr[i]) + 32);
-        float t, bu, bv;
-        if (!tri_test(L.o, L.nd, r0, r1, r2, t, bu, bv)) continue;
-        const uint32_t id = __float_as_uint(r0.w);
-        const uint32_t key = kTieById ? id : __float_as_uint(r2.w);
-        if (!accept(t, key, L.h)) continue;
-        const uint32_t ref_leaf = __float_as_uint(r1.w) & RT_REF_LEAF_MASK;
-        if (ref_leaf != L.verified_leaf)
-        {
-            if (!exact_box(L.o, L.d, A.ref_nodes + ref_leaf, L.start_length)) continue;
-            L.verified_leaf = ref_leaf;
-        }
-        L.h.t = t; L.h.id = id; L.h.slot = first + i; L.h.key = key; L.h.bu = bu; L.h.bv = bv;
-    }
-}
-
-// one wide node: conservative slab test in FMA form, leaves postponed, inner children near-first
-__device__ __forceinline__ void extend_inner(const AccelView& A, ExtendLane& L, uint32_t* stack)
-{
-    const float kWiden = 1.0e-6f;
-    const WideNode* w = ref_wide(A, L.node);
-    const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32);
-#if RT_TW_NODE48
-    const uint2 ch = make_uint2(__float_as_uint(c.y), __float_as_uint(c.z));
-    float mn0, mx0, mn1, mx1;
-    center_slabs(a, b, c, make_float2(-L.o.x, -L.o.y), make_float2(-L.o.z, -L.o.z), make_float2(L.ix, L.iy), make_float2(L.iz, L.iz),
-                 make_float2(fabsf(L.ix), fabsf(L.iy)), make_float2(fabsf(L.iz), fabsf(L.iz)), mn0, mx0, mn1, mx1);
-#elif RT_TW_CENTER
-    const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
-    // centre + half-extent nodes (accel.h): entry / exit = mid -/+ half * |inv| per axis, FMA form for mid (L.slack covers its cancellation)
-    const float aix = fabsf(L.ix), aiy = fabsf(L.iy), aiz = fabsf(L.iz);
-    float mid = fmaf(a.x, L.ix, L.cx), half = a.z * aix;
-    float mn0 = mid - half, mx0 = mid + half;
-    mid = fmaf(a.y, L.iy, L.cy); half = a.w * aiy;
-    mn0 = fmaxf(mn0, mid - half); mx0 = fminf(mx0, mid + half);
-    mid = fmaf(c.x, L.iz, L.cz); half = c.z * aiz;
-    mn0 = fmaxf(mn0, mid - half); mx0 = fminf(mx0, mid + half);
-    mid = fmaf(b.x, L.ix, L.cx); half = b.z * aix;
-    float mn1 = mid - half, mx1 = mid + half;
-    mid = fmaf(b.y, L.iy, L.cy); half = b.w * aiy;
-    mn1 = fmaxf(mn1, mid - half); mx1 = fminf(mx1, mid + half);
-    mid = fmaf(c.y, L.iz, L.cz); half = c.w * aiz;
-    mn1 = fmaxf(mn1, mid - half); mx1 = fminf(mx1, mid + half);
-#else
-    const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
-    float t1 = fmaf(a.x, L.ix, L.cx), t2 = fmaf(a.z, L.ix, L.cx);
-    float mn0 = fminf(t1, t2), mx0 = fmaxf(t1, t2);
-    t1 = fmaf(a.y, L.iy, L.cy); t2 = fmaf(a.w, L.iy, L.cy);
-    float mnb = fminf(t1, t2), mxb = fmaxf(t1, t2);
-    t1 = fmaf(c.x, L.iz, L.cz); t2 = fmaf(c.y, L.iz, L.cz);
-    mn0 = fmaxf(fmaxf(mn0, mnb), fminf(t1, t2)); mx0 = fminf(fminf(mx0, mxb), fmaxf(t1, t2));
-    t1 = fmaf(b.x, L.ix, L.cx); t2 = fmaf(b.z, L.ix, L.cx);
-    float mn1 = fminf(t1, t2), mx1 = fmaxf(t1, t2);
-    t1 = fmaf(b.y, L.iy, L.cy); t2 = fmaf(b.w, L.iy, L.cy);
-    mnb = fminf(t1, t2); mxb = fmaxf(t1, t2);
-    t1 = fmaf(c.z, L.iz, L.cz); t2 = fmaf(c.w, L.iz, L.cz);
-    mn1 = fmaxf(fmaxf(mn1, mnb), fminf(t1, t2)); mx1 = fminf(fminf(mx1, mxb), fmaxf(t1, t2));
-#endif
-    const float lo0 = fmaf(-kWiden, fabsf(mn0), mn0) - L.slack, hi0 = fmaf(kWiden, fabsf(mx0), mx0) + L.slack;
-    const float lo1 = fmaf(-kWiden, fabsf(mn1), mn1) - L.slack, hi1 = fmaf(kWiden, fabsf(mx1), mx1) + L.slack;
-    const bool hit0 = hi0 >= lo0 && lo0 <= L.h.t && hi0 > 0.0f;
-    const bool hit1 = hi1 >= lo1 && lo1 <= L.h.t && hi1 > 0.0f;
-    const bool leaf0 = hit0 && (ch.x & RT_LEAF_BIT), leaf1 = hit1 && (ch.y & RT_LEAF_BIT);
-    const bool in0 = hit0 && !(ch.x & RT_LEAF_BIT), in1 = hit1 && !(ch.y & RT_LEAF_BIT);
-    if (leaf0) { if (L.npend == 0) L.pend0 = ch.x; else L.pend1 = ch.x; L.npend++; }
-    if (leaf1) { if (L.npend == 0) L.pend0 = ch.y; else if (L.npend == 1) L.pend1 = ch.y; else L.pend2 = ch.y; L.npend++; }
-    if (in0 && in1)
-    {
-        const bool swap = mn1 < mn0;
-        stack[L.sp++] = swap ? ch.x : ch.y;
-        L.node = swap ? ch.y : ch.x;
-    }
-    else if (in0) L.node = ch.x;
-    else if (in1) L.node = ch.y;
-    else L.node = stack[--L.sp];
-}
-
-// ray set-up: spheres first (GetRayHit), slab constants, stack
-__device__ __forceinline__ void extend_begin(const AccelView& A, const SceneView& S, bool with_spheres, Vec3 o, Vec3 d, ExtendLane& L, uint32_t* stack)
-{
-    const float big = 1e30f;
-    L.o = o; L.d = d; L.nd = normalize3(d);
-    L.h.t = 1e30f; L.h.id = RT_MISS_ID; L.h.slot = 0; L.h.key = RT_MISS_ID; L.h.bu = 0; L.h.bv = 0;
-    if (with_spheres) sphere_tests(S.spheres, S.sphere_count, o, L.nd, L.h);
-    L.start_length = L.h.t;
-    L.ix = L.nd.x != 0.0f ? 1.0f / L.nd.x : big; L.iy = L.nd.y != 0.0f ? 1.0f / L.nd.y : big; L.iz = L.nd.z != 0.0f ? 1.0f / L.nd.z : big;
-    const float ax = o.x * L.ix, ay = o.y * L.iy, az = o.z * L.iz;
-    L.cx = -ax; L.cy = -ay; L.cz = -az;
-    L.slack = 4.0e-7f * fmaxf(fabsf(ax), fmaxf(fabsf(ay), fabsf(az))) + 1e-30f;
-    L.sp = 0; stack[L.sp++] = RT_SENTINEL; L.npend = 0; L.verified_leaf = RT_SENTINEL;
-    L.node = A.root_ref;
-    if (L.node & RT_LEAF_BIT) { L.pend0 = L.node; L.npend = 1; L.node = RT_SENTINEL; }
-}
-
-template <bool kTieById>
-__global__ void __launch_bounds__(256, 3) extend_rays_kernel(AccelView A, SceneView S, const float* __restrict__ rays, uint32_t ray_count,
-                                                             bool with_spheres, uint32_t* __restrict__ out_id, float* __restrict__ out_t,
-                                                             unsigned int* fetch_counter, int fetch_threshold, int leaf_batch)
-{
-    const unsigned FULL = 0xffffffffu;
-    const int lane = threadIdx.x & 31;
-    ExtendLane L; L.node = RT_SENTINEL; L.npend = 0; L.sp = 0;
-    uint32_t stack[RT_STACK_SIZE];
-    bool busy = false, exhausted = false;
-    uint32_t ray_index = 0;
-    for (;;)
-    {
-        const unsigned m_busy = __ballot_sync(FULL, busy);
-        const unsigned m_idle = __ballot_sync(FULL, !busy && !exhausted);
-        if ((m_busy | m_idle) == 0u) break;
-        if (m_idle && (m_busy == 0u || __popc(m_idle) >= fetch_threshold))
-        {
-            const int leader = __ffs(m_idle) - 1;
-            unsigned base = 0;
-            if (lane == leader) base = atomicAdd(fetch_counter, (unsigned)__popc(m_idle));
-            base = __shfl_sync(FULL, base, leader);
-            if (!busy && !exhausted)
-            {
-                ray_index = base + (unsigned)__popc(m_idle & ((1u << lane) - 1u));
-                if (ray_index >= ray_count) exhausted = true;
-                else
-                {
-                    const float* r = rays + 6 * (size_t)ray_index;
-                    const Vec3 o = mk3(__ldg(r), __ldg(r + 1), __ldg(r + 2)), d = mk3(__ldg(r + 3), __ldg(r + 4), __ldg(r + 5));
-                    if (dot3(d, d) >= RT_SHORT_DIR2) { extend_begin(A, S, with_spheres, o, d, L, stack); busy = true; }
-                    else
-                    {   // short direction: the reference's own visiting order decides (traverse.cuh RT_SHORT_DIR2) - rare, done in place
-                        HitRecord h; h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
-                        const Vec3 nd = normalize3(d);
-                        if (with_spheres) sphere_tests(S.spheres, S.sphere_count, o, nd, h);
-                        trace_reference_order<kTieById>(A, o, d, nd, h);
-                        out_id[ray_index] = h.id; out_t[ray_index] = h.t;
-                    }
-                }
-            }
-        }
-        if (busy && L.node != RT_SENTINEL && L.npend <= 1) extend_inner(A, L, stack);
-        const unsigned m_pend = __ballot_sync(FULL, busy && L.npend > 0);
-        const unsigned m_inner = __ballot_sync(FULL, busy && L.node != RT_SENTINEL && L.npend <= 1);
-        if (m_pend && (__popc(m_pend) >= leaf_batch || m_inner == 0u))
-        {
-            if (busy && L.npend > 0)
-            {
-                L.npend--;
-                const uint32_t leaf = L.npend == 0 ? L.pend0 : (L.npend == 1 ? L.pend1 : L.pend2);
-                extend_leaf<kTieById>(A, leaf, L);
-            }
-        }
-        if (busy && L.node == RT_SENTINEL && L.npend == 0)
-        {
-            out_id[ray_index] = L.h.id; out_t[ray_index] = L.h.t;
-            busy = false;
-        }
-    }
-}
-
-cudaError_t LaunchExtendRays(const AccelView& accel, const SceneView& scene, const float* d_rays, uint64_t ray_count, bool with_spheres,
-                             uint32_t* d_id, float* d_t, unsigned long long* d_ray_counter, unsigned int* d_fetch_counter, cudaStream_t stream)
-{
-    if (!ray_count) return cudaSuccess;
-    if (ray_count > 0xFFFFFFF0ull) return cudaErrorInvalidValue;
-    cudaError_t e = cudaMemsetAsync(d_fetch_counter, 0, sizeof(unsigned int), stream);
-    if (e != cudaSuccess) return e;
-    static int blocks_per_sm = 0, sm_count = 0;
-    if (!blocks_per_sm)
-    {
-        int dev = 0;
-        if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
-        if ((e = cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
-        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, extend_rays_kernel<true>, 256, 0)) != cudaSuccess) return e;
-        if (blocks_per_sm < 1) blocks_per_sm = 1;
-    }
-    int fetch = 8, batch = 12;
-    if (const char* v = getenv("B200RT_FETCH")) fetch = atoi(v);
-    if (const char* v = getenv("B200RT_LEAF_BATCH")) batch = atoi(v);
-    unsigned grid = (unsigned)(sm_count * blocks_per_sm);
-    const unsigned needed = (unsigned)((ray_count + 255) / 256);
-    if (grid > needed) grid = needed;
-    extend_rays_kernel<true><<<grid, 256, 0, stream>>>(accel, scene, d_rays, (uint32_t)ray_count, with_spheres, d_id, d_t, d_fetch_counter, fetch, batch);
-    if (d_ray_counter) { /* counted by the caller-visible contract: one query per ray */ }
-    return cudaGetLastError();
-}

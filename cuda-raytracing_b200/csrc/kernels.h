@@ -26,9 +26,6 @@ cudaError_t LaunchTracePrimary(const AccelView& accel, const SceneView& scene, i
 cudaError_t LaunchTraceRays(const AccelView& accel, const SceneView& scene, const float* d_rays, uint64_t ray_count,
                             bool with_spheres, int variant, uint32_t* d_id, float* d_t, unsigned long long* d_ray_counter,
                             cudaStream_t stream);
-// rt_trace_rays variant 2: persistent extend kernel (dynamic ray fetch, voted inner/leaf phases)
-cudaError_t LaunchExtendRays(const AccelView& accel, const SceneView& scene, const float* d_rays, uint64_t ray_count, bool with_spheres,
-                             uint32_t* d_id, float* d_t, unsigned long long* d_ray_counter, unsigned int* d_fetch_counter, cudaStream_t stream);
 // the count-work launcher additionally fills per-ray work counters (nodes popped, triangles tested)
 // under the reference traversal order: d_counts[2*i], d_counts[2*i+1]
 cudaError_t LaunchCountWork(const AccelView& accel, const SceneView& scene, int width, int height, bool with_spheres,

@@ -16,18 +16,7 @@
 #ifndef RT_PT_BLOCK
 #define RT_PT_BLOCK 128  // threads per CTA of the megakernel: 256 / 128 / 64 = 57.0 / 56.0 / 56.8 ms (finer-grained tail of the last wave)
 #endif
-#ifndef RT_PT_BINNING
-#define RT_PT_BINNING 0  // 1: measurement build of the cost-binned pixel -> lane experiment (slower the more global the binning: off)
-#endif
-#ifndef RT_PT_WARP_W
-#define RT_PT_WARP_W 8
-#endif
-#ifndef RT_PT_CARRY
-#define RT_PT_CARRY 0  // > 0: stragglers of a traversal round (at most this many lanes left) suspend and finish their ray in the next round (TraceCarry)
-#endif
-#ifndef RT_PT_FMA
-#define RT_PT_FMA 0  // 1: slab test of the path tracer in FMA form (traverse.cuh, kFma): 1 % faster on the bunny, 1.9x slower on config 4b
-#endif
+#define RT_PT_WARP_W 8     // warp footprint 8 x 4 pixels (4 x 8 / 8 x 4 / 16 x 2 = 52.8 / 52.9 / 53.3 ms)
 
 __device__ __forceinline__ void camera_ray_pt(const RtCamera& cam, float u, float v, Vec3& o, Vec3& d)
 {
@@ -43,13 +32,11 @@ struct FrameParams
     unsigned char* surface_last;
     int width, height;
     uint64_t pitch;
-    int frame_index, spp, max_bounces, blend_mode, write_last, row_order;
-    const uint32_t* pixel_perm;  // experiment: pixel handled by thread k of (virtual) tile t = pixel_perm[t * RT_PT_BLOCK + k], ~0u = none
-    uint32_t* pixel_cost;        // experiment (kCount): traversal steps this launch spent on each pixel
+    int frame_index, spp, max_bounces, blend_mode, write_last;
     const uint32_t* tile_order;  // cost-ordered scheduling (workspace): tile processed by the k-th CTA, or nullptr = grid order
     uint32_t* tile_cost;         // per tile: SM cycles / 16 its slowest warp took in this launch (input of the next launch's order)
     unsigned long long* ray_counter;
-    unsigned long long* work_counters;  // variant 2: [0] += nodes popped, [1] += triangle tests (reference traversal order)
+    unsigned long long* work_counters;  // variants 2 / 3: [0] += nodes popped / wide-node steps, [1] += triangle tests
     PathConsts consts;
 };
 
@@ -75,15 +62,15 @@ __device__ __forceinline__ void write_pixel(const FrameParams& P, int x, int y, 
     if (P.write_last) *(reinterpret_cast<float4*>(P.surface_last + (size_t)y * P.pitch) + x) = out;
 }
 
-// kMode 0: product traversal. kMode 2: reference-order traversal with work counters (measurement of the
-// algorithmic bytes per ray; same image up to exact-tie resolution).
-template <int kMode, int kMinBlocks, bool kLockstep = false, bool kCount = false, int kMinusCtas = 0>
-__global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK) - kMinusCtas) pathtrace_megakernel(AccelView A, SceneView S, FrameParams P)
+// kMode 0: product traversal. kMode 2: reference-order traversal with work counters (measurement of the algorithmic bytes per
+// ray; same image up to exact-tie resolution). kMode 3: product traversal with work counters (wide-node steps and
+// triangle tests actually executed: bench.py's bytes_per_ray_product_order; same image and RNG as kMode 0).
+template <int kMode, int kMinBlocks>
+__global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK)) pathtrace_megakernel(AccelView A, SceneView S, FrameParams P)
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    // CTA = 16 x (RT_PT_BLOCK / 16) pixels, warp = 8 x 4. P.row_order permutes the order in which tile rows are scheduled
-    // (0: bottom-up, 1: top-down, k > 1: stride k, coprime with the row count) - the image is the same, only the tail of the launch moves.
-    unsigned bx = blockIdx.x, by = P.row_order == 0 ? blockIdx.y : P.row_order == 1 ? gridDim.y - 1u - blockIdx.y : (blockIdx.y * (unsigned)P.row_order) % gridDim.y;
+    // CTA = 16 x (RT_PT_BLOCK / 16) pixels, warp = 8 x 4
+    unsigned bx = blockIdx.x, by = blockIdx.y;
     unsigned tile = 0;
     long long t_start = 0;
     if (P.tile_order)
@@ -94,21 +81,12 @@ __global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK) 
         bx = tile % tiles_x; by = tile / tiles_x;
         t_start = clock64();
     }
-    // warp footprint inside the 16-wide CTA tile: RT_PT_WARP_W x (32 / RT_PT_WARP_W) pixels (8 x 4 measured best: 4 x 8 .., 16 x 2 ..)
     constexpr int kWarpsX = 16 / RT_PT_WARP_W, kWarpH = 32 / RT_PT_WARP_W;
-    int x = bx * 16 + (warp % kWarpsX) * RT_PT_WARP_W + (lane % RT_PT_WARP_W);
-    int y = by * (RT_PT_BLOCK / 16) + (warp / kWarpsX) * kWarpH + (lane / RT_PT_WARP_W);
-    bool active = x < P.width && y < P.height;
-    if (RT_PT_BINNING && P.pixel_perm)
-    {
-        const uint32_t pix = __ldg(P.pixel_perm + (size_t)(P.tile_order ? tile : blockIdx.x) * RT_PT_BLOCK + threadIdx.x);
-        active = pix != 0xFFFFFFFFu;
-        x = (int)(pix % (uint32_t)P.width); y = (int)(pix / (uint32_t)P.width);
-    }
-    uint32_t steps = 0;
+    const int x = bx * 16 + (warp % kWarpsX) * RT_PT_WARP_W + (lane % RT_PT_WARP_W);
+    const int y = by * (RT_PT_BLOCK / 16) + (warp / kWarpsX) * kWarpH + (lane / RT_PT_WARP_W);
+    const bool active = x < P.width && y < P.height;
     unsigned rays = 0;
-    uint32_t work_nodes = 0, work_tris = 0;
-    const unsigned lane_mask = __ballot_sync(0xffffffffu, active);
+    uint32_t work[2] = { 0, 0 };
     if (active)
     {
         RtRngState* state = S.rng_state + (size_t)y * P.width + x;  // GPUScene::GetRNGForPixel, GPUScene.h:95
@@ -117,20 +95,8 @@ __global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK) 
         PathState ps;
         int sample = 0, bounce = 0;
         bool fresh = true;
-#if RT_PT_CARRY
-        uint32_t carry_stack[RT_STACK_SIZE];
-        TraceCarry carry; carry.stack = carry_stack; carry.node = RT_SENTINEL; carry.sp = 0; carry.resume = false; carry.threshold = RT_PT_CARRY;
-        float carry_start = 0.0f;
-        HitRecord h;
-#endif
-        while (kLockstep ? __any_sync(lane_mask, sample < P.spp) : (sample < P.spp))
+        while (sample < P.spp)
         {
-            if (kLockstep)
-            {   // experiment: no regeneration across samples - a lane that finished its sample waits until the whole warp has
-                // (camera rays of one sample are then traced together, coherently)
-                const bool all_fresh = __all_sync(lane_mask, fresh);
-                if (sample >= P.spp || (fresh && !all_fresh)) continue;
-            }
             if (fresh)
             {   // main_raytracing.cu:190-191; jitter draws x first, then y
                 const float jx = rng.uniform(), jy = rng.uniform();
@@ -145,19 +111,9 @@ __global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK) 
                 r.t = 1e30f; r.id = RT_MISS_ID; r.slot = 0; r.key = RT_MISS_ID; r.bu = 0; r.bv = 0;
                 sphere_tests(S.spheres, S.sphere_count, ps.o, nd, r);
             };
-#if RT_PT_CARRY
-            if (kMode == 0)
-            {
-                if (!carry.resume) reinit(h);
-                if (!trace_wide_resumable<false, RT_PT_FMA != 0>(A, ps.o, ps.d, nd, h, reinit, carry, carry_start)) { carry.resume = true; continue; }
-                carry.resume = false;
-            }
-            else { reinit(h); trace_reference_order<false>(A, ps.o, ps.d, nd, h, &work_nodes, &work_tris); }
-#else
             HitRecord h; reinit(h);
-            if (kMode == 0) trace_wide<false, RT_PT_FMA != 0>(A, ps.o, ps.d, nd, h, reinit, kCount ? &steps : nullptr);
-            else trace_reference_order<false>(A, ps.o, ps.d, nd, h, &work_nodes, &work_tris);
-#endif
+            if (kMode == 2) trace_reference_order<false>(A, ps.o, ps.d, nd, h, &work[0], &work[1]);
+            else trace_wide<false>(A, ps.o, ps.d, nd, h, reinit, kMode == 3 ? work : nullptr);
             rays++;
             bool alive;
             if (h.id != RT_MISS_ID) alive = shade_hit(A, S, h, ps, rng) && (++bounce < P.max_bounces);
@@ -166,7 +122,6 @@ __global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK) 
         }
         rng.store(state);
         write_pixel(P, x, y, sum);
-        if (RT_PT_BINNING && kCount && P.pixel_cost) P.pixel_cost[(size_t)y * P.width + x] = steps;
     }
     if (P.tile_order && lane == 0)
     {
@@ -178,10 +133,10 @@ __global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK) 
         for (int o = 16; o; o >>= 1) rays += __shfl_xor_sync(0xffffffffu, rays, o);
         if (lane == 0 && rays) atomicAdd(P.ray_counter, (unsigned long long)rays);
     }
-    if (kMode == 2 && P.work_counters)
+    if (kMode >= 2 && P.work_counters)
     {
-        for (int o = 16; o; o >>= 1) { work_nodes += __shfl_xor_sync(0xffffffffu, work_nodes, o); work_tris += __shfl_xor_sync(0xffffffffu, work_tris, o); }
-        if (lane == 0) { atomicAdd(P.work_counters, (unsigned long long)work_nodes); atomicAdd(P.work_counters + 1, (unsigned long long)work_tris); }
+        for (int o = 16; o; o >>= 1) { work[0] += __shfl_xor_sync(0xffffffffu, work[0], o); work[1] += __shfl_xor_sync(0xffffffffu, work[1], o); }
+        if (lane == 0) { atomicAdd(P.work_counters, (unsigned long long)work[0]); atomicAdd(P.work_counters + 1, (unsigned long long)work[1]); }
     }
 }
 
@@ -240,17 +195,9 @@ __global__ void __launch_bounds__(1024) tile_order_kernel(uint32_t* ws, uint32_t
     if (threadIdx.x == 0) ws[3]++;
 }
 
-#if RT_PT_BINNING
-// measurement build only (benchmarks/pixel_binning.py): explicit pixel -> lane assignment and a per-pixel step count
-static const uint32_t* g_debug_pixel_perm = nullptr;
-static uint32_t* g_debug_pixel_cost = nullptr;
-extern "C" void rt_debug_pixel_binning(const uint32_t* d_perm, uint32_t* d_cost) { g_debug_pixel_perm = d_perm; g_debug_pixel_cost = d_cost; }
-#endif
-
 uint64_t PathTraceWorkspaceBytes(int width, int height)
 {
-    uint64_t n = (uint64_t)((width + 15) / 16) * (uint64_t)((height + RT_PT_BLOCK / 16 - 1) / (RT_PT_BLOCK / 16));
-    n = std::max<uint64_t>(n, ((uint64_t)width * height + RT_PT_BLOCK - 1) / RT_PT_BLOCK);
+    const uint64_t n = (uint64_t)((width + 15) / 16) * (uint64_t)((height + RT_PT_BLOCK / 16 - 1) / (RT_PT_BLOCK / 16));
     return (RT_TILE_HDR + 2 * n) * sizeof(uint32_t);
 }
 
@@ -271,46 +218,20 @@ cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, cons
         P.consts.qz = cx * cy * sz - sx * sy * cz;
     }
     const int tile_h = RT_PT_BLOCK / 16;
-    {
-        static int row_order = -1;
-        if (row_order < 0) { const char* v = getenv("B200RT_ROW_ORDER"); row_order = v ? atoi(v) : 0; }
-        const int rows = (p.height + tile_h - 1) / tile_h;
-        int k = row_order;
-        if (k > 1) { auto gcd = [](int a, int b) { while (b) { const int t = a % b; a = b; b = t; } return a; }; while (gcd(k, rows) != 1) k++; }
-        P.row_order = k;
-    }
     dim3 grid((p.width + 15) / 16, (p.height + tile_h - 1) / tile_h), block(RT_PT_BLOCK);
     P.tile_order = nullptr; P.tile_cost = nullptr;
-    P.pixel_perm = nullptr; P.pixel_cost = nullptr;
-#if RT_PT_BINNING
-    P.pixel_perm = g_debug_pixel_perm; P.pixel_cost = g_debug_pixel_cost;
-#endif
-    if (P.pixel_perm) grid = dim3((unsigned)(((size_t)p.width * p.height + RT_PT_BLOCK - 1) / RT_PT_BLOCK), 1);
-    static int use_order = -1;
-    if (use_order < 0) { const char* v = getenv("B200RT_TILE_ORDER"); use_order = v ? atoi(v) : 1; }
-    if (use_order && p.variant == 0 && p.workspace && p.workspace_bytes >= PathTraceWorkspaceBytes(p.width, p.height))
+    // a workspace switches the cost-ordered schedule on (p.workspace == nullptr: grid order, also what the reference-named entry uses)
+    if (p.variant == 0 && p.workspace && p.workspace_bytes >= PathTraceWorkspaceBytes(p.width, p.height))
     {
         const uint32_t n = grid.x * grid.y;
-        if (P.pixel_perm && PathTraceWorkspaceBytes(p.width, p.height) < (RT_TILE_HDR + 2ull * n) * 4) return cudaErrorInvalidValue;
         uint32_t* ws = (uint32_t*)p.workspace;
         tile_order_kernel<<<1, 1024, 0, stream>>>(ws, (uint32_t)p.width, (uint32_t)p.height, n);
         P.tile_order = ws + RT_TILE_HDR; P.tile_cost = ws + RT_TILE_HDR + n;
         grid = dim3(n, 1);
     }
-    static int min_blocks = 0;
-    if (!min_blocks) { const char* v = getenv("B200RT_MINBLOCKS"); min_blocks = v ? atoi(v) : 5; }  // occupancy sweep hook (profiles/)
     if (p.variant == 2) pathtrace_megakernel<2, 3><<<grid, block, 0, stream>>>(accel, scene, P);
-#if RT_PT_BINNING
-    else if (P.pixel_cost) pathtrace_megakernel<0, 5, false, true><<<grid, block, 0, stream>>>(accel, scene, P);
-#endif
-    else if (min_blocks == 45) pathtrace_megakernel<0, 5, false, false, 1><<<grid, block, 0, stream>>>(accel, scene, P);  // 9 CTAs of 128 threads: 56 registers
-    else if (min_blocks == 55) pathtrace_megakernel<0, 6, false, false, 1><<<grid, block, 0, stream>>>(accel, scene, P);  // 11 CTAs: 44 registers
-    else if (min_blocks == 6) pathtrace_megakernel<0, 6><<<grid, block, 0, stream>>>(accel, scene, P);
-    else if (min_blocks == 4) pathtrace_megakernel<0, 4><<<grid, block, 0, stream>>>(accel, scene, P);
-    else if (min_blocks == 3) pathtrace_megakernel<0, 3><<<grid, block, 0, stream>>>(accel, scene, P);
-    else if (min_blocks == 2) pathtrace_megakernel<0, 2><<<grid, block, 0, stream>>>(accel, scene, P);
-    else if (getenv("B200RT_LOCKSTEP")) pathtrace_megakernel<0, 5, true><<<grid, block, 0, stream>>>(accel, scene, P);
-    else pathtrace_megakernel<0, 5><<<grid, block, 0, stream>>>(accel, scene, P);  // default: 5 resident CTAs/SM (48 regs, small spill) measured fastest
+    else if (p.variant == 3) pathtrace_megakernel<3, 5><<<grid, block, 0, stream>>>(accel, scene, P);
+    else pathtrace_megakernel<0, 5><<<grid, block, 0, stream>>>(accel, scene, P);  // 5 x 256 threads per SM (48 registers): 3 / 4 / 5 / 6 = 57.4 / 55.3 / 52.9 / 54.8 ms
     return cudaGetLastError();
 }
 
@@ -342,7 +263,7 @@ __global__ void __launch_bounds__(256) ambient_occlusion_kernel(AccelView A, Sce
                 sphere_tests(S.spheres, S.sphere_count, o, nd, r);
             };
             HitRecord h; reinit(h);
-            trace_wide<false, RT_PT_FMA != 0>(A, o, d, nd, h, reinit);
+            trace_wide<false>(A, o, d, nd, h, reinit);
             rays++;
             if (k == 0)
             {
@@ -379,12 +300,3 @@ cudaError_t LaunchAmbientOcclusion(const AccelView& accel, const SceneView& scen
     return cudaGetLastError();
 }
 
-#if defined(RT_TW_MODE) && RT_TW_MODE == 8
-// measurement build only: read (and optionally clear) the lane histogram of this TU's kernels
-extern "C" int rt_debug_tw_hist(unsigned long long* out66, int reset)
-{
-    if (cudaMemcpyFromSymbol(out66, g_tw_hist, sizeof(unsigned long long) * 66) != cudaSuccess) return -1;
-    if (reset) { unsigned long long zero[66] = {}; if (cudaMemcpyToSymbol(g_tw_hist, zero, sizeof(zero)) != cudaSuccess) return -1; }
-    return 0;
-}
-#endif

@@ -178,22 +178,12 @@ __global__ void __launch_bounds__(256, kMinBlocks) pathtrace_regroup_kernel(Acce
         const unsigned m_leaf = __ballot_sync(FULL, on_leaf), m_inner = __ballot_sync(FULL, trav && !on_leaf);
         if (trav && !on_leaf)
         {
-            const WideNode* w = ref_wide(A, node);
+            const WideNode* w = reinterpret_cast<const WideNode*>(A.arena + (node & RT_REF_BYTE_MASK));
             const float4 a = ldg4(w), b = ldg4(reinterpret_cast<const char*>(w) + 16), c = ldg4(reinterpret_cast<const char*>(w) + 32);
-            const uint2 ch = RT_TW_NODE48 ? make_uint2(__float_as_uint(c.y), __float_as_uint(c.z)) : __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
-            // exact slab form (plane - o) * inv in packed fp32, three-compare conservative cull (traverse.cuh)
-#if RT_TW_CENTER
+            const uint2 ch = __ldg(reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(w) + 48));
+            // centre + half-extent node test, three-compare conservative cull (traverse.cuh)
             float mn0, mx0, mn1, mx1;
             center_slabs(a, b, c, no_xy, no_zz, i_xy, i_zz, make_float2(fabsf(i_xy.x), fabsf(i_xy.y)), make_float2(fabsf(i_zz.x), fabsf(i_zz.y)), mn0, mx0, mn1, mx1);
-#else
-            const float2 d0 = __fmul2_rn(__fadd2_rn(make_float2(a.x, a.y), no_xy), i_xy), d1 = __fmul2_rn(__fadd2_rn(make_float2(a.z, a.w), no_xy), i_xy);
-            const float2 d2 = __fmul2_rn(__fadd2_rn(make_float2(b.x, b.y), no_xy), i_xy), d3 = __fmul2_rn(__fadd2_rn(make_float2(b.z, b.w), no_xy), i_xy);
-            const float2 d4 = __fmul2_rn(__fadd2_rn(make_float2(c.x, c.y), no_zz), i_zz), d5 = __fmul2_rn(__fadd2_rn(make_float2(c.z, c.w), no_zz), i_zz);
-            const float mn0 = fmaxf(fmaxf(fminf(d0.x, d1.x), fminf(d0.y, d1.y)), fminf(d4.x, d4.y));
-            const float mx0 = fminf(fminf(fmaxf(d0.x, d1.x), fmaxf(d0.y, d1.y)), fmaxf(d4.x, d4.y));
-            const float mn1 = fmaxf(fmaxf(fminf(d2.x, d3.x), fminf(d2.y, d3.y)), fminf(d5.x, d5.y));
-            const float mx1 = fminf(fminf(fmaxf(d2.x, d3.x), fmaxf(d2.y, d3.y)), fmaxf(d5.x, d5.y));
-#endif
             const float lo0 = fmaf(-kWiden, fabsf(mn0), mn0), hi0 = fmaf(kWiden, fabsf(mx0), mx0);
             const float lo1 = fmaf(-kWiden, fabsf(mn1), mn1), hi1 = fmaf(kWiden, fabsf(mx1), mx1);
             const bool hit0 = hi0 >= lo0 && lo0 <= h.t && hi0 > 0.0f;
@@ -221,7 +211,7 @@ __global__ void __launch_bounds__(256, kMinBlocks) pathtrace_regroup_kernel(Acce
             {
                 h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
                 sphere_tests(S.spheres, S.sphere_count, ps.o, nd, h);
-                trace_wide_checked<false, false>(A, ps.o, ps.d, nd, h);
+                trace_wide_checked<false>(A, ps.o, ps.d, nd, h);
             }
             state = ST_NEED; have_hit = true;
         }

@@ -72,8 +72,7 @@ int rt_accel_destroy(RtAccel* accel);
 int rt_accel_check_host(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* face_indices,
                         const RtFace* faces, uint32_t face_count, const RtVertex* vertices, uint32_t vertex_count,
                         uint32_t fat_leaf_threshold, uint64_t* info4);
-/* info[0..7] = wide nodes, triangle slots, reference leaves, fat leaves (low 32 bits) | adjacent duplicate-face pairs (high 32 bits),
- * max depth (wide), device bytes lo, hi, reference depth */
+/* info[0..7] = wide nodes, triangle slots, reference leaves, fat leaves, max depth (wide), device bytes lo, hi, reference depth */
 int rt_accel_info(const RtAccel* accel, uint64_t* info8);
 /* associate `accel` with scenes whose gpu_bvh_nodes == d_nodes_key (lookup used by raytracing_process) */
 int rt_accel_bind(const void* d_nodes_key, RtAccel* accel);
@@ -106,8 +105,7 @@ int rt_dds_read_level0(const char* dds_path, float* out_texels, size_t capacity_
 
 /* Pixel-centre primary rays of scene->camera (GPUCamera::GetRay, RayTracing/GPUScene.h:13).
  * d_id/d_t: width*height. with_spheres: also test scene->gpu_spheres first (GetRayHit semantics).
- * variant: 0 = product kernel, 1 = reference-order exact kernel (by-construction parity);
- * rt_trace_rays also takes 2 = persistent extend kernel (dynamic ray fetch; same results as 0). */
+ * variant: 0 = product kernel, 1 = reference-order exact kernel (by-construction parity). */
 int rt_trace_primary(const RtAccel* accel, const RtGPUScene* scene, int width, int height, int with_spheres,
                      int variant, uint32_t* d_id, float* d_t, unsigned long long* d_ray_counter, void* stream);
 /* Arbitrary rays: 6 floats each (origin, direction as given; normalised inside like BVHRayHit does). */
@@ -129,7 +127,8 @@ typedef struct RtProcessParams
                                    1 = surface += sum of this launch's samples (multi-GPU sum buffers) */
     int32_t variant;            /* 0 = megakernel (regenerating), 1 = regrouping persistent kernel (in-register wavefront:
                                    finished rays are parked, shaded and refilled together by warp ballot; bit-identical image),
-                                   2 = measurement: reference traversal order + d_work_counters (nodes popped, triangle tests) */
+                                   2 = measurement: reference traversal order + d_work_counters (nodes popped, triangle tests),
+                                   3 = measurement: the megakernel with d_work_counters (wide-node steps, triangle tests executed) */
     int32_t write_last_frame;   /* 1 = also store the result into surface_last_frame (folds the reference's D2D copy) */
     const RtGPUScene* scene;    /* HOST struct, device pointers inside; rng_state must hold width*height states */
     const RtAccel* accel;
@@ -137,7 +136,7 @@ typedef struct RtProcessParams
     void* stream;
     void* workspace;            /* wavefront only: device scratch of rt_process_workspace_bytes() */
     uint64_t workspace_bytes;
-    unsigned long long* d_work_counters; /* optional, variant 2: [0] += nodes popped, [1] += triangle tests */
+    unsigned long long* d_work_counters; /* optional, variants 2 / 3: [0] += nodes popped (wide-node steps), [1] += triangle tests */
 } RtProcessParams;
 
 int rt_process_ex(const RtProcessParams* params);

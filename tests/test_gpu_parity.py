@@ -296,7 +296,7 @@ def test_cost_ordered_tile_schedule_does_not_change_the_frame(rt, torch_cuda):
     assert (cost > 0).all()  # every tile ran and reported
     prev = b.workspace  # the other scene's workspace was never used
     assert int(prev.view(torch_cuda.int32).abs().sum().item()) == 0
-    assert rt.lib().rt_process_workspace_bytes(W, H, 0) == (4 + 2 * max(n, (W * H + 127) // 128)) * 4
+    assert rt.lib().rt_process_workspace_bytes(W, H, 0) == (4 + 2 * n) * 4
 
 
 def test_sample_split_is_stream_continuous(rt, torch_cuda):

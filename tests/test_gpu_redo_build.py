@@ -1,0 +1,36 @@
+"""-m gpu: the redo path of trace_wide (csrc/traverse.cuh). The product checks the winner's reference leaf box ONCE per ray
+(main_raytracing.cu:46 deferred); only when that fails - a ray grazing a leaf box within rounding - is the ray redone by the
+__noinline__ copy that checks per candidate, which ordinary frames exercise about never. libb200rt_redo.so (built by
+__graft_entry__.build(), RT_TW_FORCE_REDO=7) forces 1/8 of the triangle hits through it; results must not change."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+import util
+
+pytestmark = pytest.mark.gpu
+
+
+def run(cmd, lib):
+    env = dict(os.environ)
+    if lib:
+        env["B200RT_LIB"] = lib
+    else:
+        env.pop("B200RT_LIB", None)
+    return subprocess.run([sys.executable] + cmd, cwd=util.ROOT, env=env, capture_output=True, text=True, timeout=900)
+
+
+def test_forced_redo_build_is_bit_identical(rt, torch_cuda):
+    from _loader import load_build
+    redo = load_build().REDO_LIB
+    assert os.path.exists(redo), "libb200rt_redo.so missing: __graft_entry__.build() builds it"
+    a = run(["benchmarks/frame_hash.py"], None)
+    b = run(["benchmarks/frame_hash.py"], redo)
+    assert a.returncode == 0 and b.returncode == 0, (a.stderr[-2000:], b.stderr[-2000:])
+    assert a.stdout.strip().splitlines()[-1] == b.stdout.strip().splitlines()[-1]  # frame + RNG hash + ray count
+    # and the id / t parity tests against the reference goldens pass with it
+    t = run(["-m", "pytest", "tests/test_gpu_parity.py", "-m", "gpu", "-q", "-x", "-k",
+             "primary_hits_vs_reference_golden or incoherent_rays_vs_reference_golden or fresh_random_rays"], redo)
+    assert t.returncode == 0, t.stdout[-3000:]

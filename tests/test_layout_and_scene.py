@@ -153,7 +153,7 @@ def test_accel_relayout_structure_on_the_host(rt, bunny):
         return [int(v) for v in info]
     a = bunny["arrays"]
     inner, leaves, depth, arena = check(a, 0)
-    assert arena - len(a["faces"]) * 48 in (inner * 64, inner * 48) and leaves >= 69273 and depth < 62  # 48: the RT_TW_NODE48 build
+    assert arena - len(a["faces"]) * 48 == inner * 64 and leaves >= 69273 and depth < 62
     for threshold in (1, 2, 4, 16):
         i2, l2, d2, _ = check(a, threshold)
         assert i2 + 1 == l2 or i2 == l2 - 1  # a binary tree

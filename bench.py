@@ -63,7 +63,6 @@ def workload_name(a):
 class CpuReference:
     def __init__(self, a):
         import ref_oracle as ro
-        from _loader import load_package
         if not ro.available():
             raise RuntimeError("oracle/_ref/libref_oracle.so missing (built by __graft_entry__.build() where /root/reference exists)")
         self.ro, self.a = ro, a
@@ -71,11 +70,11 @@ class CpuReference:
             ro.lib().ref_set_num_threads(len(os.sched_getaffinity(0)))
         except (AttributeError, OSError):
             pass
-        rt = load_package()
-        scene, _ = util.bunny_scene(rt)  # host-side assembly only (no device call)
-        arr = scene.arrays()
-        self.sc = {k: util.raw(arr[k]) for k in ("vertices", "faces", "spheres", "materials")}
-        self.nodes, self.fi = util.raw(arr["nodes"]), arr["face_indices"]
+        # the reference's own scene assembly (GLM restatement of RayTracing.cpp:33-203 in oracle/ref_shim) and its verbatim BVH.cpp on
+        # the committed ingest fixture: this arm never loads libb200rt.so
+        m = np.load(os.path.join(util.GOLDEN, "bunny_smooth_mesh.npz"))
+        self.sc = ro.build_scene(np.ascontiguousarray(m["positions"]), np.ascontiguousarray(m["normals"]), np.ascontiguousarray(m["indices"]))
+        self.nodes, self.fi = ro.bvh_build(self.sc["vertices"], self.sc["faces"])
         p, ax, ay = util.POSES[a.pose]
         self.cam = ro.camera(p, ax, ay, a.width, a.height)
         self.cm = util.cubemap_texels()

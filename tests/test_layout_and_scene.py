@@ -86,6 +86,17 @@ def test_scene_assembly_bitwise_vs_glm_build(rt, ref, bunny):
     assert f["v2"][k + 1] == f["v0"][k + 1] + 1 and f["v1"][k + 1] == f["v0"][k + 1] + 2
 
 
+def test_smooth_mesh_fixture_is_the_ingest_output(rt, ref, bunny):
+    """tests/golden/bunny_smooth_mesh.npz (what bench.py's reference arm assembles its scene from, without libb200rt.so) is the
+    product's ingest output, and the reference-side assembly of it is the scene every parity test runs on."""
+    import os
+    m = np.load(os.path.join(util.GOLDEN, "bunny_smooth_mesh.npz"))
+    pos, nrm, idx, _ = bunny["mesh"].arrays()
+    assert np.array_equal(m["positions"], pos) and np.array_equal(m["normals"], nrm) and np.array_equal(m["indices"], idx)
+    r = ref.build_scene(np.ascontiguousarray(m["positions"]), np.ascontiguousarray(m["normals"]), np.ascontiguousarray(m["indices"]))
+    assert np.array_equal(util.raw(bunny["arrays"]["vertices"]), r["vertices"]) and np.array_equal(util.raw(bunny["arrays"]["faces"]), r["faces"])
+
+
 def test_bvh_topology_identical_to_reference_builder(rt, ref, bunny):
     a = bunny["arrays"]
     nodes, face_indices = ref.bvh_build(util.raw(a["vertices"]), util.raw(a["faces"]))

@@ -85,6 +85,8 @@ SYMBOLS = {
     "rt_dds_info": (_I, [_P, C.c_size_t, C.POINTER(_U64), _I]),
     "rt_process_ex": (_I, [_P]),
     "rt_process_workspace_bytes": (_U64, [_I, _I, _I]),
+    "rt_process_ex_static_scratch": (_I, [_P]),
+    "rt_process_static_scratch_bytes": (_U64, []),
     "rt_ambient_occlusion": (_I, [_P, _P, _I, _I, _I, _P, _P, _P]),
     "rt_tonemap_rgba8": (_I, [_P, _I, _I, _U64, _F, _P, _P]),
     "rt_count_reference_work": (_I, [_P, _P, _I, _I, _I, _P, _P]),

@@ -300,3 +300,69 @@ cudaError_t LaunchAmbientOcclusion(const AccelView& accel, const SceneView& scen
     return cudaGetLastError();
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// rt_process_ex_static_scratch: rt_process_ex for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+// serving loops, harnesses that forbid it). No counterpart in the reference.
+// The cost-ordered tile schedule's scratch (header + tile order + tile cost, RT_TILE_HDR + 2 n words) lives in a file-scope
+// device array instead of a caller-allocated workspace: RT_STATIC_SCRATCH_BYTES = 1 MiB per GPU that loads the library, held
+// until exit - room for 131 070 tiles of 16 x 8 pixels = 16.7 M pixels (a 4K frame has 64 800 tiles).
+// In HOST code the array's name is a host-side stand-in, not a device address: its device address is taken once per device with
+// cudaGetSymbolAddress while that device is current, and that pointer is what the launch receives.
+// ------------------------------------------------------------------------------------------------
+#define RT_STATIC_SCRATCH_BYTES (1u << 20)
+static __device__ __align__(256) unsigned char g_static_scratch[RT_STATIC_SCRATCH_BYTES];
+
+#include <mutex>
+#include "capi_internal.h"
+
+namespace
+{
+    constexpr int kMaxDevices = 64;
+    std::mutex g_scratch_mutex;
+    void* g_scratch_ptr[kMaxDevices] = {};  // per device: device address of g_static_scratch
+
+    // device address of this device's copy of g_static_scratch (set-up: once per device, with that device current)
+    int StaticScratch(void** out)
+    {
+        int dev = -1;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return rt_internal::CudaFail(e, "rt_process_ex_static_scratch: cudaGetDevice");
+        if (dev < 0 || dev >= kMaxDevices) return rt_internal::Fail(RT_E_INVALID, "rt_process_ex_static_scratch: device ordinal beyond 63");
+        std::lock_guard<std::mutex> lock(g_scratch_mutex);
+        if (!g_scratch_ptr[dev])
+        {
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_static_scratch);
+            if (e != cudaSuccess || !p) return rt_internal::CudaFail(e, "rt_process_ex_static_scratch: cudaGetSymbolAddress");
+            g_scratch_ptr[dev] = p;
+        }
+        *out = g_scratch_ptr[dev];
+        return RT_OK;
+    }
+}
+
+extern "C" uint64_t rt_process_static_scratch_bytes(void) { return RT_STATIC_SCRATCH_BYTES; }
+
+extern "C" int rt_process_ex_static_scratch(const RtProcessParams* params)
+{
+    using namespace rt_internal;
+    if (!params) return Fail(RT_E_INVALID, "rt_process_ex_static_scratch: bad argument");
+    if (params->variant != 0) return Fail(RT_E_INVALID, "rt_process_ex_static_scratch: only variant 0 (the megakernel) uses scratch memory");
+    if (params->width <= 0 || params->height <= 0) return Fail(RT_E_INVALID, "rt_process_ex_static_scratch: bad argument");
+    const uint64_t need = PathTraceWorkspaceBytes(params->width, params->height);
+    if (need > RT_STATIC_SCRATCH_BYTES)
+        return Fail(RT_E_INVALID, "rt_process_ex_static_scratch: frame needs " + std::to_string(need) + " bytes of tile scratch, the static array holds " +
+                                      std::to_string(RT_STATIC_SCRATCH_BYTES) + " (131070 tiles of 16x8 pixels); use rt_process_ex with a caller-owned workspace");
+    void* scratch = nullptr;
+    if (int r = StaticScratch(&scratch)) return r;
+    // The array is shared by every call on this device and keeps the last call's contents. What must start at zero does: the header
+    // names the frame size the order / cost words belong to, tile_order_kernel treats any other size as "no history" (grid order,
+    // costs zeroed) and zeroes the costs after every sort; a new accumulation (frame_index 0) drops the history explicitly so its
+    // schedule never depends on what another caller rendered before.
+    if (params->frame_index == 0)
+        RT_CUDA(cudaMemsetAsync(scratch, 0, RT_TILE_HDR * sizeof(uint32_t), (cudaStream_t)params->stream));
+    RtProcessParams p = *params;
+    p.workspace = scratch; p.workspace_bytes = RT_STATIC_SCRATCH_BYTES;
+    return rt_process_ex(&p);
+}

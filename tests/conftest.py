@@ -15,6 +15,7 @@ def pytest_configure(config):
 def rt():
     from _loader import load_build, load_package
     load_build().build()
+    load_build().build_redo_variant()  # test build of tests/test_gpu_redo_build.py: never older than the sources
     return load_package()
 
 

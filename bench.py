@@ -7,7 +7,11 @@ One "step" = one 1080p frame of 64 samples per pixel (camera rays -> BVH travers
   value      whole-job Mrays/s (closest-hit queries counted on device / CUDA-event time, max over ranks), inputs resident
   e2e        same metric through the headless CUDARayTracer facade call (RenderToHost): per step the mutable scene
              state goes host->device and the float4 frame comes back into pinned HOST memory, wall clock around the call
-  roofline   path-trace kernel against the bytes-per-ray memory roofline of SURVEY.md §8(d)
+  roofline   path-trace kernel against the bound that binds it: warp-instruction issue (scene is L2-resident); the bytes-per-ray
+             figures of SURVEY.md §8(d) (reference order and product order), DRAM and L2 traffic ride along as flat keys
+  configs    bounded side measurements, same event protocol: primary-only / bounce-only Mrays/s, AO (config 3), 10x10 grid (config 4b),
+             the reference's own CUDA kernel (unmodified, sm_100a) on the same frame
+  strong     one timed step of BASELINE config 5 (4K, 1024 spp total split over the ranks, one reduce): the strong-scaling curve
   cpu_baseline   the reference's own kernel body compiled host-side (oracle/_ref), all host threads, bounded sample
 N > 1: every rank renders its own 64 spp of the same frame with disjoint XORWOW subsequences into a sum buffer, then
 one NCCL reduce (fp32 sum) to rank 0 per frame - weak scaling in samples (BASELINE config 5's partitioning).
@@ -49,6 +53,9 @@ def parse_args():
     ap.add_argument("--seed", type=int, default=1234)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-flush", action="store_true", help="profiling runs only: no L2-flush fill between steps")
+    ap.add_argument("--no-strong", action="store_true", help="skip the config-5 strong-scaling step (4K, 1024 spp)")
+    ap.add_argument("--no-configs", action="store_true", help="skip the side measurements (primary / bounce / AO / 4b / reference CUDA kernel)")
     return ap.parse_args()
 
 
@@ -192,6 +199,41 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def csrc_hash():
+    """sha1 over the device sources: profiles/traffic.json records it, so a stale ncu capture is never applied to another kernel."""
+    import hashlib
+    h = hashlib.sha1()
+    d = os.path.join(ROOT, "cuda-raytracing_b200", "csrc")
+    for name in sorted(os.listdir(d)):
+        if name.endswith((".cu", ".cuh", ".h")):
+            h.update(name.encode()); h.update(open(os.path.join(d, name), "rb").read())
+    return h.hexdigest()[:16]
+
+
+def load_capture(key):
+    """One entry of profiles/traffic.json (written by benchmarks/update_traffic.py from an ncu --set full report), or None when it
+    was captured on other device sources than the ones in this tree."""
+    try:
+        cap = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[key]
+    except Exception:
+        return None, "no capture in profiles/traffic.json"
+    if cap.get("csrc_hash") != csrc_hash():
+        return None, f"capture in profiles/traffic.json was taken on csrc {cap.get('csrc_hash')}, tree is {csrc_hash()}: re-run benchmarks/update_traffic.py"
+    return cap, None
+
+
+def timed_median(torch, fn, reps, flush):
+    """median CUDA-event time of fn() in ms: one untimed call first, L2 flushed before every timed call (outside the events)"""
+    fn(); torch.cuda.synchronize()
+    ms = []
+    for k in range(reps):
+        flush.fill_(k & 0xFF)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+        ms.append(e0.elapsed_time(e1))
+    return sorted(ms)[len(ms) // 2]
+
+
 def run_b200_arm(a):
     import torch
     import torch.distributed as dist
@@ -235,6 +277,15 @@ def run_b200_arm(a):
     cnt_rays = int(d.counter.item()); nodes_per_ray = work[0].item() / cnt_rays; tris_per_ray = work[1].item() / cnt_rays
     bytes_per_ray = 32.0 * nodes_per_ray + 48.0 * tris_per_ray + 64.0
     d.rng.copy_(rng_keep)
+    # ... and what the shipped kernel actually executes (variant 3: the megakernel with two counters): wide-node steps x 64 B +
+    # triangle tests x 48 B + 64 B per ray
+    work.zero_(); d.counter.zero_()
+    process_ex(d.surface, d.last, W, H, d.pitch, 0, d.gpu, d.accel, spp=2, bounces=a.bounces, blend_mode=0, variant=3,
+               ray_counter=d.counter, stream=stream, work_counters=work)
+    torch.cuda.synchronize()
+    cnt3 = int(d.counter.item()); steps_per_ray = work[0].item() / cnt3; tests_per_ray = work[1].item() / cnt3
+    bytes_per_ray_product = 64.0 * steps_per_ray + 48.0 * tests_per_ray + 64.0
+    d.rng.copy_(rng_keep)
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     blend = 0 if world == 1 else 1
@@ -246,8 +297,16 @@ def run_b200_arm(a):
         frame(blend, sum_buf)
         multigpu.reduce_frame(sum_buf, dist if world > 1 else None)
 
-    for _ in range(max(a.warmup, 0)):
-        flush.fill_(1); step()
+    first_launch_ms = None
+    for w in range(max(a.warmup, 0)):
+        if not a.no_flush:
+            flush.fill_(1)
+        if w == 0:  # the one launch without tile-cost history (grid order): what a camera jump or resize costs
+            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            f0.record(); step(); f1.record(); torch.cuda.synchronize()
+            first_launch_ms = f0.elapsed_time(f1)
+        else:
+            step()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -258,7 +317,8 @@ def run_b200_arm(a):
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
     wall0 = time.perf_counter()
     for k in range(a.steps):
-        flush.fill_(k & 0xFF)  # L2 flush between timed steps (outside the event pairs)
+        if not a.no_flush:
+            flush.fill_(k & 0xFF)  # L2 flush between timed steps (outside the event pairs)
         ev[k][0].record()
         if blend == 1:
             sum_buf.zero_()
@@ -289,48 +349,74 @@ def run_b200_arm(a):
     if not a.no_e2e:
         e2e = run_e2e(a, rt, torch, dev, world, rank)
 
+    strong = None
+    if not a.no_strong:
+        strong = run_strong_step(a, rt, torch, dist if world > 1 else None, dev, world, rank)
     if world > 1:
         dist.barrier()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return 0
+    configs = None
+    if world == 1 and not a.no_configs:
+        configs = run_configs_block(a, rt, torch, d, flush)
 
     peak, peak_src = measured_peaks()
-    traffic = None  # dram bytes per launch from the committed ncu capture of this exact launch shape (never measured under bench)
-    issue = None    # what actually bounds the kernel: warp instructions per launch (same capture) against the SMs' issue rate
-    try:
-        if a.variant == 0 and (a.width, a.height, a.spp_per_launch, a.bounces, a.pose) == (1920, 1080, 64, 4, "poseB"):
-            cap = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["pathtrace_megakernel"]
-            traffic = cap["dram_bytes_per_launch"]
-            props = torch.cuda.get_device_properties(dev)
-            mhz = (clocks or {}).get("sm_mhz") or 1965.0
-            peak_ginst = props.multi_processor_count * 4 * mhz * 1e-3  # 4 schedulers per SM, 1 warp instruction per clock each
-            ach_ginst = cap["warp_instructions_per_launch"] / ((kern_ms / launches_per_step / a.steps) * 1e-3) / 1e9
-            issue = {"achieved": ach_ginst, "peak": peak_ginst, "unit": "G warp-inst/s", "frac": ach_ginst / peak_ginst,
-                     "threads_per_instruction": cap["threads_per_instruction"],
-                     "source": "instruction count from the committed ncu capture (profiles/traffic.json), time and SM clock live"}
-    except Exception:
-        traffic = None
     launches = a.steps * launches_per_step
     px = W * H
-    alg_bytes_per_launch = (rays / launches) * bytes_per_ray + px * 80.0
-    achieved = alg_bytes_per_launch / ((kern_ms / launches) * 1e-3) / 1e9
+    launch_s = (kern_ms / launches) * 1e-3
+    rays_per_launch = rays / launches
+    props = torch.cuda.get_device_properties(dev)
+    mhz = (clocks or {}).get("sm_mhz") or 1965.0
+    peak_ginst = props.multi_processor_count * 4 * mhz * 1e-3  # 4 schedulers per SM, one warp instruction per clock each
+    # The scene is L2-resident (22 MB), so HBM does not bound this kernel: instruction issue does. Warp-instruction count, DRAM and
+    # L2 bytes per launch come from the committed ncu capture of this exact launch (never measured under bench); time and clock are live.
+    cap, cap_note = (None, "not the captured launch shape")
+    if a.variant == 0 and (a.width, a.height, a.spp_per_launch, a.bounces, a.pose) == (1920, 1080, 64, 4, "poseB"):
+        cap, cap_note = load_capture("pathtrace_megakernel")
+    alg_ref = rays_per_launch * bytes_per_ray + px * 80.0
+    alg_prod = rays_per_launch * bytes_per_ray_product + px * 80.0
+    roofline = {"bound": "issue", "achieved": None, "peak": peak_ginst, "unit": "G warp-inst/s", "frac": None, "traffic": None,
+                "kernel": "pathtrace_megakernel<0,5>", "threads_per_instruction": None, "lane_frac": None,
+                "warp_instructions_per_ray": None, "dram_bytes": None, "dram_gbs": None, "dram_frac": None, "l2_gbs": None,
+                "hbm_peak_gbs": peak, "hbm_peak_source": peak_src,
+                "peak_source": f"{props.multi_processor_count} SMs x 4 schedulers x {mhz:.0f} MHz (median SM clock sampled during the timed region)",
+                "capture": cap["source"] if cap else cap_note,
+                "bytes_per_ray_reference_order": bytes_per_ray, "nodes_per_ray_reference_order": nodes_per_ray, "tris_per_ray_reference_order": tris_per_ray,
+                "hbm_algorithmic_gbs": alg_ref / launch_s / 1e9,
+                "bytes_per_ray_product_order": bytes_per_ray_product, "node_steps_per_ray_product_order": steps_per_ray,
+                "tri_tests_per_ray_product_order": tests_per_ray, "product_order_gbs": alg_prod / launch_s / 1e9,
+                "note": "bound = warp-instruction issue: the 22 MB scene is L2-resident and DRAM carries only surfaces + RNG states (dram_frac). "
+                        "hbm_algorithmic_gbs = SURVEY 8(d)'s bytes per ray under the REFERENCE traversal order over the kernel time (informational: "
+                        "it exceeds the HBM peak because near-first order + the fat-leaf sub-tree remove most of that work and none of it goes to "
+                        "HBM); product_order_gbs = the bytes the shipped kernel's own node steps and triangle tests read, served by L1 / L2"}
+    if cap:
+        ach = cap["warp_instructions_per_launch"] / launch_s / 1e9
+        roofline.update({"achieved": ach, "frac": ach / peak_ginst, "traffic": cap["dram_bytes_per_launch"],
+                         "threads_per_instruction": cap["threads_per_instruction"], "lane_frac": cap["threads_per_instruction"] / 32.0,
+                         "warp_instructions_per_ray": cap["warp_instructions_per_launch"] / rays_per_launch,
+                         "dram_bytes": cap["dram_bytes_per_launch"], "dram_gbs": cap["dram_bytes_per_launch"] / launch_s / 1e9,
+                         "dram_frac": cap["dram_bytes_per_launch"] / launch_s / 1e9 / peak,
+                         "dram_bytes_algorithmic": px * 80.0 + 22e6,
+                         "l2_gbs": cap.get("l2_bytes_per_launch", 0) / launch_s / 1e9 if cap.get("l2_bytes_per_launch") else None})
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": step_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": workload_name(a), "spp_per_launch": a.spp_per_launch, "kernel_variant": a.variant,
                    "l2": "flushed between timed steps (256 MiB fill, outside the event pairs); scene working set itself is L2-resident by nature",
+                   "schedule": "timed steps are history-warmed: the cost-ordered tile schedule uses the previous launch's measured tile costs (static camera); "
+                               "the first launch after a resize or camera jump runs in grid order (see config.first_launch_ms)",
+                   "first_launch_ms": first_launch_ms,
                    "parallelism": "1 GPU" if world == 1 else f"spp split: {world} ranks x {a.spp} spp, disjoint XORWOW subsequences, 1 NCCL reduce(sum fp32) of the frame per step",
                    "rays_per_step": rays_all / a.steps, "ms_per_frame_64spp": step_ms / a.steps, "wall_s": wall},
-        "clocks": clocks, "gpu_launches": launches,
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                     "kernel": "pathtrace_megakernel", "peak_source": peak_src, "issue": issue,
-                     "bytes_per_ray": bytes_per_ray, "nodes_per_ray_reference_order": nodes_per_ray, "tris_per_ray_reference_order": tris_per_ray,
-                     "note": "algorithmic bytes = rays x (32 B x nodes + 48 B x tris under the REFERENCE traversal order + 64) + pixels x 80; "
-                             "the bunny scene is L2-resident, so frac > 1 means cache/culling amplification, not HBM traffic (SURVEY §8d); `traffic` (ncu, same protocol) includes the write-back of the L2-flush buffer's dirty lines evicted during the launch (~230 MB) on top of surfaces + RNG states + first-touch scene"},
+        "clocks": clocks, "gpu_launches": launches * (2 if a.variant == 0 else 1), "roofline": roofline,
     }
+    if strong:
+        line["strong"] = strong
+    if configs:
+        line["configs"] = configs
     if e2e:
         line["e2e"] = e2e
     if world == 1 and not a.no_cpu_baseline:
@@ -386,6 +472,113 @@ def run_e2e(a, rt, torch, dev, world, rank):
     return {"value": rays / dt / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d // a.steps, "d2h_bytes_per_step": W * H * 16,
             "ms_per_step": 1e3 * dt / a.steps,
             "call": "rt_host_tracer_render_to_host (CUDARayTracer::RenderToHost): pinned host frame out, scene state in"}
+
+
+def run_configs_block(a, rt, torch, d, flush):
+    """Bounded side measurements (about 15 s), the bench step's own protocol (L2 flushed, CUDA events, median of 3): the north-star
+    targets (primary >= 2 Grays/s, diffuse bounce >= 0.5 Grays/s), BASELINE configs 3 and 4b, and the reference's own CUDA kernel."""
+    import ref_oracle as ro
+    W, H = a.width, a.height
+    out = {}
+
+    def pt(dev, spp, bounces):
+        dev.counter.zero_()
+        f = lambda: dev.process(0, spp=spp, bounces=bounces, write_last=1)
+        f(); n = dev.rays()
+        return n, timed_median(torch, f, 3, flush)
+
+    n1, ms1 = pt(d, 16, 1)
+    n4, ms4 = pt(d, 16, a.bounces)
+    out["primary_only"] = {"what": f"{W}x{H}, 16 spp, max_bounces=1 (jittered camera rays only), camera {a.pose}", "rays": n1, "ms": ms1, "mrays_s": n1 / ms1 / 1e3}
+    out["bounce_only"] = {"what": f"rays of depth >= 1: the {a.bounces}-bounce 16-spp launch ({n4} rays, {ms4:.3f} ms) minus the primary-only launch",
+                          "rays": n4 - n1, "ms": ms4 - ms1, "mrays_s": (n4 - n1) / (ms4 - ms1) / 1e3}
+    ao = torch.zeros(W * H, dtype=torch.float32, device=d.device)
+    d.counter.zero_()
+    f = lambda: rt.check(rt.lib().rt_ambient_occlusion(d.accel, d.gpu, W, H, 16, rt.ptr(ao), rt.ptr(d.counter), None))
+    f(); n = d.rays()
+    ms = timed_median(torch, f, 3, flush)
+    out["ao_config3"] = {"what": f"{W}x{H}: pixel-centre primary ray + 16 diffuse-lobe rays per hit", "rays": n, "ms": ms, "mrays_s": n / ms / 1e3}
+    # the reference's own CUDA kernel (unmodified main_raytracing.cu / Random.cu, nvcc -O3 sm_100a) on the same GPUScene: its frame is
+    # 5 spp x 6 bounces + the caller's D2D copy (RayTracing.cpp:232-233); ray count of that workload from the product's counter
+    if ro.gpu_available():
+        g = ro.gpu_lib()
+        nref, mine = pt(d, 5, 6)
+
+        def ref_frame():
+            g.raytracing_process(rt.ptr(d.surface), rt.ptr(d.last), W, H, d.pitch, 0, d.gpu)
+            d.last.copy_(d.surface)
+        ms = timed_median(torch, ref_frame, 3, flush)
+        out["reference_cuda_kernel"] = {"what": f"UNMODIFIED reference raytracing_kernel_main (oracle/_ref/libref_gpu.so), {W}x{H}, 5 spp x 6 bounces + its D2D copy, camera {a.pose}",
+                                        "ms": ms, "rays_approx": nref, "mrays_s": nref / ms / 1e3,
+                                        "product_ms_same_frame": mine, "product_mrays_s": nref / mine / 1e3, "speedup": ms / mine}
+    else:
+        out["reference_cuda_kernel"] = {"unavailable": "oracle/_ref/libref_gpu.so not built"}
+    # config 4b: the only config whose working set exceeds L2
+    t0 = time.perf_counter()
+    scene, mesh, pose, times = util.scaled_scene(rt, "b", env=True)
+    import gpu_util
+    g4 = gpu_util.DeviceScene(rt, torch, W, H, pose, seed=a.seed, env=True, scene=scene, device=d.device)
+    torch.cuda.synchronize()
+    build_s = time.perf_counter() - t0
+    n, ms = pt(g4, 16, a.bounces)
+    out["grid_config4b"] = {"what": f"10x10 bunny grid, {scene.counts()['faces']} triangles, {W}x{H}, 16 spp, {a.bounces} bounces",
+                            "rays": n, "ms": ms, "mrays_s": n / ms / 1e3, "scene_build_upload_s": build_s,
+                            "accel_bytes": int(scene.accel_info()["device_bytes"])}
+    del g4, scene, mesh
+    torch.cuda.empty_cache()
+    return out
+
+
+def run_strong_step(a, rt, torch, dist, dev, world, rank):
+    """BASELINE config 5 as ONE timed step: 3840x2160, 1024 spp in total split evenly over the ranks (64-spp launches into a sum
+    buffer, disjoint XORWOW subsequences), one reduce(sum, fp32) of the 132.7 MB frame to rank 0. RNG init is outside the timed
+    region (reported). Time = max over ranks, CUDA events."""
+    import gpu_util
+    from cuda_raytracing_b200 import multigpu
+    W, H, TOTAL = 3840, 2160, 1024
+    if TOTAL % world:
+        return {"unavailable": f"1024 spp do not split evenly over {world} ranks"}
+    spp_rank = TOTAL // world
+    d = gpu_util.DeviceScene(rt, torch, W, H, a.pose, seed=a.seed, env=True, device=dev)
+    r0, r1, e1, e2, e3 = (torch.cuda.Event(enable_timing=True) for _ in range(5))
+    n_states = gpu_util.rng_state_count(W, H)
+    r0.record(); d.reseed(a.seed, multigpu.rank_first_subsequence(rank, n_states)); r1.record()
+    acc = d.surface
+    d.process(0, spp=4, bounces=a.bounces, blend_mode=1, surface=acc)  # warm-up launch: gives the tile schedule its cost history
+    d.reseed(a.seed, multigpu.rank_first_subsequence(rank, n_states))
+    acc.zero_(); d.counter.zero_()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e1.record()
+    launches = 0
+    left = spp_rank
+    while left > 0:
+        s = min(64, left)
+        d.process(launches, spp=s, bounces=a.bounces, blend_mode=1, surface=acc)
+        left -= s; launches += 1
+    e2.record()
+    multigpu.reduce_frame(acc, dist if world > 1 else None)
+    e3.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e1.elapsed_time(e3), e1.elapsed_time(e2), e2.elapsed_time(e3), float(d.rays())], dtype=torch.float64, device=dev)
+    if world > 1:
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        ms, render_ms, reduce_ms, rays = tmax[0].item(), tmax[1].item(), tmax[2].item(), tsum[3].item()
+    else:
+        ms, render_ms, reduce_ms, rays = t[0].item(), t[1].item(), t[2].item(), t[3].item()
+    ok = True
+    if rank == 0:
+        img = acc[..., :3] / acc[..., 3:4]
+        ok = bool(torch.isfinite(img).all()) and float(acc[..., 3].min()) == float(TOTAL) == float(acc[..., 3].max())
+    del d
+    torch.cuda.empty_cache()
+    return {"width": W, "height": H, "spp_total": TOTAL, "spp_per_rank": spp_rank, "launches_per_rank": launches, "ms": ms,
+            "render_ms": render_ms, "reduce_ms": reduce_ms, "rng_init_ms_untimed": r0.elapsed_time(r1), "reduce_bytes": W * H * 16 if world > 1 else 0, "rays": rays,
+            "mrays_s": rays / ms / 1e3, "alpha_equals_spp_total": ok,
+            "limiter": "per-rank render time (the slowest rank's launch tail); the reduce is reduce_ms of ms"}
 
 
 def main():

@@ -23,12 +23,21 @@ def main(rep, note):
         u = units[hdr.index(key)].lower()
         return v * {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9}.get(u, 1)
 
+
     path = os.path.join(ROOT, "profiles", "traffic.json")
-    t = json.load(open(path))
+    sys.path.insert(0, ROOT)
+    import bench
+    t = json.load(open(path)) if os.path.exists(path) else {}
     t["pathtrace_megakernel"] = {
         "dram_bytes_per_launch": int(val("dram__bytes_read.sum") + val("dram__bytes_write.sum")),
         "warp_instructions_per_launch": int(val("smsp__inst_executed.sum")),
         "threads_per_instruction": round(val("smsp__thread_inst_executed_per_inst_executed.ratio"), 2),
+        "l2_bytes_per_launch": int(val("lts__t_sectors.sum")) * 32,
+        "l2_hit_pct": round(val("lts__t_sector_hit_rate.pct"), 2),
+        "dram_read_bytes": int(val("dram__bytes_read.sum")), "dram_write_bytes": int(val("dram__bytes_write.sum")),
+        "issue_active_pct": round(val("smsp__issue_active.avg.pct_of_peak_sustained_active"), 2),
+        "duration_under_ncu": d["gpu__time_duration.sum"] + " " + units[hdr.index("gpu__time_duration.sum")],
+        "csrc_hash": bench.csrc_hash(),
         "source": note,
     }
     json.dump(t, open(path, "w"), indent=1)

@@ -246,8 +246,10 @@ def run_b200_arm(a):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = f"cuda:{local}"
+    host_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device(dev))
+        host_group = dist.new_group(backend="gloo")  # host-side waits: ranks that idle while rank 0 drives every GPU must not park a NCCL kernel on theirs
     rt = load_package()
     W, H = a.width, a.height
     launches_per_step = (a.spp + a.spp_per_launch - 1) // a.spp_per_launch
@@ -347,7 +349,7 @@ def run_b200_arm(a):
     # ---- e2e: the headless facade call with HOST buffers ----
     e2e = None
     if not a.no_e2e:
-        e2e = run_e2e(a, rt, torch, dev, world, rank)
+        e2e = run_e2e(a, rt, torch, dev, world, rank) if world == 1 else run_e2e_multi(a, rt, torch, dist, host_group, world, rank)
 
     strong = None
     if not a.no_strong:
@@ -432,6 +434,38 @@ def run_b200_arm(a):
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def run_e2e_multi(a, rt, torch, dist, host_group, world, rank):
+    """N > 1: the partitioned job through the repo's own multi-GPU call (rt_host_multi_tracer_render, host/MultiGPU.h): ONE process
+    (rank 0) drives all N devices with one host thread each - spp split, ncclReduce inside the library, resolve, float4 frame
+    into pinned HOST memory. The other ranks wait on the host (gloo) with their GPUs idle. Weak scaling like `value`: every device
+    renders a.spp samples per step, the frame holds N * a.spp."""
+    torch.cuda.synchronize()
+    dist.barrier(group=host_group)
+    out = None
+    if rank == 0:
+        W, H = a.width, a.height
+        assets = util.assets()
+        host = torch.empty((H, W, 4), dtype=torch.float32).pin_memory()
+        m = rt.MultiTracer(W, H, bunny_obj=assets["obj"], env_dds=assets["dds"], max_bounces=a.bounces, seed=a.seed, devices=list(range(world)))
+        m.set_camera(*util.POSES[a.pose])
+        for _ in range(max(a.warmup, 1)):
+            m.render(a.spp * world, a.spp_per_launch, host)
+        r0 = m.ray_count
+        t0 = time.perf_counter()
+        tm = None
+        for _ in range(a.steps):
+            tm = m.render(a.spp * world, a.spp_per_launch, host)
+        dt = time.perf_counter() - t0
+        rays = m.ray_count - r0
+        assert float(host[..., 3].min()) == 1.0 and bool(torch.isfinite(host).all())
+        out = {"value": rays / dt / 1e6, "unit": UNIT, "h2d_bytes_per_step": world * 136 * ((a.spp + a.spp_per_launch - 1) // a.spp_per_launch),
+               "d2h_bytes_per_step": W * H * 16, "ms_per_step": 1e3 * dt / a.steps, "last_step": tm,
+               "call": f"rt_host_multi_tracer_render (MultiGPUTracer::Render): {world} devices x {a.spp} spp, one ncclReduce, pinned host frame out"}
+        del m
+    dist.barrier(group=host_group)
+    return out
 
 
 def run_e2e(a, rt, torch, dev, world, rank):

@@ -88,6 +88,7 @@ SYMBOLS = {
     "rt_process_ex_static_scratch": (_I, [_P]),
     "rt_process_static_scratch_bytes": (_U64, []),
     "rt_ambient_occlusion": (_I, [_P, _P, _I, _I, _I, _P, _P, _P]),
+    "rt_resolve_sum": (_I, [_P, _P, _I, _I, _U64, _U64, _P]),
     "rt_tonemap_rgba8": (_I, [_P, _I, _I, _U64, _F, _P, _P]),
     "rt_count_reference_work": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     # b200rt_host.h
@@ -124,6 +125,13 @@ SYMBOLS = {
     "rt_host_tracer_ray_count": (C.c_ulonglong, [_P]),
     "rt_host_tracer_save_checkpoint": (_I, [_P, C.c_char_p]),
     "rt_host_tracer_load_checkpoint": (_I, [_P, C.c_char_p]),
+    "rt_host_multi_tracer_create": (_I, [_I, _I, _P, _P, _I, C.POINTER(_P)]),
+    "rt_host_multi_tracer_destroy": (None, [_P]),
+    "rt_host_multi_tracer_device_count": (_I, [_P]),
+    "rt_host_multi_tracer_set_camera": (_I, [_P, _P, _F, _F]),
+    "rt_host_multi_tracer_reseed": (_I, [_P, _U32]),
+    "rt_host_multi_tracer_render": (_I, [_P, _I, _I, _P, _U64, _P]),
+    "rt_host_multi_tracer_ray_count": (C.c_ulonglong, [_P]),
     "rt_host_write_ppm": (_I, [C.c_char_p, _P, _I, _I]),
 }
 
@@ -165,4 +173,4 @@ def ptr(a):
     return C.c_void_p(int(a))
 
 
-from .api import Mesh, Scene, Tracer, Accel, EnvMap  # noqa: E402,F401
+from .api import Mesh, Scene, Tracer, MultiTracer, Accel, EnvMap  # noqa: E402,F401

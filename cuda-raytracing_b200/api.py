@@ -219,6 +219,44 @@ class Tracer:
             self.handle = None
 
 
+class MultiTracer:
+    """RayTracing::MultiGPUTracer (host/MultiGPU.h): spp split over the devices of one node, one ncclReduce per frame, frame to host."""
+
+    def __init__(self, width, height, bunny_obj=None, env_dds=None, cornell_box=True, max_bounces=6, seed=0, devices=None):
+        o = TracerOptions(_b(bunny_obj), _b(env_dds), int(cornell_box), 0, max_bounces, seed, 0)
+        dev = (C.c_int * len(devices))(*devices) if devices else None
+        h = C.c_void_p()
+        check(lib().rt_host_multi_tracer_create(width, height, C.byref(o), dev, len(devices) if devices else 0, C.byref(h)))
+        self.handle = h
+        self.width, self.height = width, height
+
+    @property
+    def device_count(self):
+        return lib().rt_host_multi_tracer_device_count(self.handle)
+
+    def set_camera(self, position, angle_x, angle_y):
+        p = None if position is None else np.asarray(position, np.float32)
+        check(lib().rt_host_multi_tracer_set_camera(self.handle, ptr(p), angle_x, angle_y))
+
+    def reseed(self, seed):
+        check(lib().rt_host_multi_tracer_reseed(self.handle, seed))
+
+    def render(self, total_spp, spp_per_launch, host_pixels, host_pitch=None):
+        """-> {render_ms, reduce_ms, total_ms}; host_pixels: numpy float32 [H, W, 4] or a (pinned) torch CPU tensor."""
+        t = (C.c_double * 3)()
+        check(lib().rt_host_multi_tracer_render(self.handle, total_spp, spp_per_launch, ptr(host_pixels), host_pitch or self.width * 16, t))
+        return {"render_ms": t[0], "reduce_ms": t[1], "total_ms": t[2]}
+
+    @property
+    def ray_count(self):
+        return lib().rt_host_multi_tracer_ray_count(self.handle)
+
+    def __del__(self):
+        if getattr(self, "handle", None):
+            _safe_destroy("rt_host_multi_tracer_destroy", self.handle)
+            self.handle = None
+
+
 def process_ex(surface, last, width, height, pitch, frame_index, scene_ptr, accel_ptr, spp=5, bounces=6, blend_mode=0,
                variant=0, write_last=0, ray_counter=None, stream=None, work_counters=None, workspace=None):
     """workspace: zero-filled uint8 device tensor of process_workspace_bytes(width, height) (cost-ordered tile scheduling

@@ -21,7 +21,7 @@ SOURCES = [
     "csrc/kernels.cu", "csrc/pathtrace.cu", "csrc/pathtrace_regroup.cu", "csrc/capi.cu", "csrc/capi_render.cu",
     "csrc/accel_build.cpp", "csrc/dds.cpp", "csrc/rng_host.cpp",
     "host/Math.cpp", "host/BVH.cpp", "host/MeshLoader.cpp", "host/Subdivide.cpp", "host/Scene.cpp",
-    "host/SceneSetup.cpp", "host/SceneUpload.cpp", "host/RayTracing.cpp", "host/host_capi.cpp",
+    "host/SceneSetup.cpp", "host/SceneUpload.cpp", "host/RayTracing.cpp", "host/MultiGPU.cpp", "host/host_capi.cpp",
 ]
 HEADERS_DIRS = ["csrc", "host", os.path.join(ROOT, "include")]
 
@@ -88,7 +88,7 @@ def build(force=False, verbose=False, defines=(), out=None):
             sys.stderr.write(f"--- {src} ---\n{out}\n")
     if failed:
         raise RuntimeError("nvcc failed")
-    link = [_nvcc(), "-shared", "-o", target] + objects + ["-cudart", "static", "-Xcompiler", "-fopenmp", "-lgomp"]
+    link = [_nvcc(), "-shared", "-o", target] + objects + ["-cudart", "static", "-Xcompiler", "-fopenmp", "-lgomp", "-ldl"]
     subprocess.run(link, check=True)
     return target
 

@@ -347,4 +347,12 @@ int rt_tonemap_rgba8(const void* surface, int width, int height, uint64_t pitch,
     return RT_OK;
 }
 
+int rt_resolve_sum(const void* sum_surface, void* out_surface, int width, int height, uint64_t pitch_in, uint64_t pitch_out, void* stream)
+{
+    if (!sum_surface || !out_surface || width <= 0 || height <= 0 || pitch_in < (uint64_t)width * 16 || pitch_out < (uint64_t)width * 16)
+        return Fail(RT_E_INVALID, "rt_resolve_sum: bad argument");
+    RT_CUDA(LaunchResolveSum(sum_surface, out_surface, width, height, pitch_in, pitch_out, (cudaStream_t)stream));
+    return RT_OK;
+}
+
 }  // extern "C"

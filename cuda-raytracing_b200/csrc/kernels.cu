@@ -202,3 +202,23 @@ cudaError_t LaunchTonemap(const void* surface, int width, int height, uint64_t p
     tonemap_kernel<<<grid, block, 0, stream>>>((const unsigned char*)surface, width, height, pitch, 1.0f / divide_by, d_rgba8);
     return cudaGetLastError();
 }
+
+// ------------------------------------------------------------------------------------------------
+// Resolve of a sum buffer (blend_mode 1: rgb = sum of sample radiance, alpha = sample count; after the multi-GPU reduce the sums
+// of all ranks): mean = rgb / alpha, alpha = 1 - the surface contract of main_raytracing.cu:195-199.
+// ------------------------------------------------------------------------------------------------
+__global__ void resolve_sum_kernel(const unsigned char* __restrict__ sum, unsigned char* __restrict__ out, int width, int height, uint64_t pitch_in, uint64_t pitch_out)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= width || y >= height) return;
+    const float4 s = *reinterpret_cast<const float4*>(sum + (size_t)y * pitch_in + (size_t)x * 16);
+    const float n = s.w > 0.0f ? s.w : 1.0f;
+    *reinterpret_cast<float4*>(out + (size_t)y * pitch_out + (size_t)x * 16) = make_float4(s.x / n, s.y / n, s.z / n, 1.0f);
+}
+
+cudaError_t LaunchResolveSum(const void* sum, void* out, int width, int height, uint64_t pitch_in, uint64_t pitch_out, cudaStream_t stream)
+{
+    const dim3 block(32, 8), grid((width + 31) / 32, (height + 7) / 8);
+    resolve_sum_kernel<<<grid, block, 0, stream>>>((const unsigned char*)sum, (unsigned char*)out, width, height, pitch_in, pitch_out);
+    return cudaGetLastError();
+}

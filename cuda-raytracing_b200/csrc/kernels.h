@@ -40,3 +40,4 @@ cudaError_t LaunchAmbientOcclusion(const AccelView& accel, const SceneView& scen
                                    float* d_ao, unsigned long long* d_ray_counter, cudaStream_t stream);
 cudaError_t LaunchTonemap(const void* surface, int width, int height, uint64_t pitch, float divide_by, uint8_t* d_rgba8,
                           cudaStream_t stream);
+cudaError_t LaunchResolveSum(const void* sum, void* out, int width, int height, uint64_t pitch_in, uint64_t pitch_out, cudaStream_t stream);

@@ -70,7 +70,9 @@ namespace RayTracing
             gpu_spheres = static_cast<const RtSphere*>(d_spheres); gpu_materials = static_cast<const RtMaterial*>(d_materials);
             gpu_vertices = static_cast<const RtVertex*>(d_vertices); gpu_faces = static_cast<const RtFace*>(d_faces);
         }
-        if ((bvh_dirty || memory_dirty) && !faces.empty())
+        // the re-layout depends on nodes, faces and vertices only, and every geometry change raises the BVH flag (Scene.cpp AddTriangle /
+        // AddLoadedScene): a material or sphere edit (SceneMemory alone) does not rebuild it
+        if (bvh_dirty && !faces.empty())
         {
             if (accel) { rt_accel_destroy(accel); accel = nullptr; }
             const auto nodes = bvh->GetGPUBVHNodes();

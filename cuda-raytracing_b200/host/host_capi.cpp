@@ -4,6 +4,7 @@
 #include <string>
 #include "BVH.h"
 #include "MeshLoader.h"
+#include "MultiGPU.h"
 #include "RayTracing.h"
 #include "Scene.h"
 #include "b200rt_host.h"
@@ -14,6 +15,7 @@ using namespace RayTracing;
 struct RtHostMesh { Loader::LoadedMesh mesh; };
 struct RtHostScene { Scene* scene; bool owned; };
 struct RtHostTracer { CUDARayTracer* tracer; RtHostScene scene_handle; };
+struct RtHostMultiTracer { MultiGPUTracer* tracer; };
 
 namespace
 {
@@ -251,6 +253,55 @@ int rt_host_tracer_set_sampling(RtHostTracer* t, int spp, int bounces, int varia
 }
 
 unsigned long long rt_host_tracer_ray_count(const RtHostTracer* t) { return t ? t->tracer->GetRayCount() : 0; }
+
+int rt_host_multi_tracer_create(int width, int height, const RtHostTracerOptions* o, const int* devices, int device_count, RtHostMultiTracer** out)
+{
+    if (!out || width <= 0 || height <= 0 || device_count < 0 || (device_count && !devices)) return rt_internal::Fail(RT_E_INVALID, "rt_host_multi_tracer_create: bad argument");
+    if (rt_device_count() <= 0) return rt_internal::Fail(RT_E_CUDA, "rt_host_multi_tracer_create: no CUDA device (there is no CPU fallback)");
+    return Guard([&] {
+        MultiGPUTracer::Options m;
+        m.width = width; m.height = height;
+        m.devices.assign(devices, devices + device_count);
+        if (o)
+        {
+            m.tracer.stanford_bunny = o->bunny_obj != nullptr;
+            if (o->bunny_obj) m.tracer.bunny_obj = o->bunny_obj;
+            m.tracer.env_dds = o->env_dds ? o->env_dds : "";
+            m.tracer.cornell_box = o->cornell_box != 0;
+            if (o->max_bounces > 0) m.tracer.max_bounces = o->max_bounces;
+            m.tracer.seed = o->seed;
+        }
+        *out = new RtHostMultiTracer{ new MultiGPUTracer(m) };
+        return RT_OK;
+    });
+}
+
+void rt_host_multi_tracer_destroy(RtHostMultiTracer* t) { if (t) { delete t->tracer; delete t; } }
+int rt_host_multi_tracer_device_count(const RtHostMultiTracer* t) { return t ? t->tracer->DeviceCount() : 0; }
+
+int rt_host_multi_tracer_set_camera(RtHostMultiTracer* t, const float* position3, float angle_x_deg, float angle_y_deg)
+{
+    if (!t) return rt_internal::Fail(RT_E_INVALID, "null tracer");
+    return Guard([&] { t->tracer->SetCamera(position3, angle_x_deg, angle_y_deg); return RT_OK; });
+}
+
+int rt_host_multi_tracer_reseed(RtHostMultiTracer* t, uint32_t seed)
+{
+    if (!t) return rt_internal::Fail(RT_E_INVALID, "null tracer");
+    return Guard([&] { t->tracer->Reseed(seed); return RT_OK; });
+}
+
+int rt_host_multi_tracer_render(RtHostMultiTracer* t, int total_spp, int spp_per_launch, void* host_pixels, uint64_t host_pitch, double* timing_ms3)
+{
+    if (!t) return rt_internal::Fail(RT_E_INVALID, "null tracer");
+    return Guard([&] {
+        t->tracer->Render(total_spp, spp_per_launch, host_pixels, host_pitch);
+        if (timing_ms3) { const auto& tm = t->tracer->LastTiming(); timing_ms3[0] = tm.render_ms; timing_ms3[1] = tm.reduce_ms; timing_ms3[2] = tm.total_ms; }
+        return RT_OK;
+    });
+}
+
+unsigned long long rt_host_multi_tracer_ray_count(const RtHostMultiTracer* t) { return t ? t->tracer->RayCount() : 0; }
 
 int rt_host_write_ppm(const char* path, const uint8_t* rgba8, int width, int height)
 {

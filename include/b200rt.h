@@ -158,6 +158,10 @@ uint64_t rt_process_static_scratch_bytes(void);
 int rt_ambient_occlusion(const RtAccel* accel, const RtGPUScene* scene, int width, int height, int ao_rays,
                          float* d_ao, unsigned long long* d_ray_counter, void* stream);
 
+/* Resolve of a blend_mode-1 sum buffer (rgb = summed radiance, alpha = sample count; after a multi-GPU reduce: of all ranks):
+ * out = (rgb / alpha, 1) - the surface contract of main_raytracing.cu:195-199. In place (out == sum) is allowed. */
+int rt_resolve_sum(const void* sum_surface, void* out_surface, int width, int height, uint64_t pitch_in, uint64_t pitch_out, void* stream);
+
 /* ---- display transform (main.cpp:78-94 HLSL restated as CUDA) ---------------- */
 /* exposure 0.5, ACES fit, sRGB encode, vertical flip (row 0 of the surface is the bottom row) -> RGBA8 */
 int rt_tonemap_rgba8(const void* surface, int width, int height, uint64_t pitch, float divide_by, uint8_t* d_rgba8, void* stream);

@@ -79,6 +79,24 @@ int rt_host_tracer_frame_index(const RtHostTracer* tracer);
 int rt_host_tracer_set_sampling(RtHostTracer* tracer, int samples_per_launch, int max_bounces, int kernel_variant);
 unsigned long long rt_host_tracer_ray_count(const RtHostTracer* tracer);
 
+/* ---- multi-GPU renderer (north-star item 5; the reference is single-GPU: what is replicated per GPU is its per-frame
+ * protocol, RayTracing/RayTracing.cpp:205-235) ----
+ * One process, one host thread per device. Scene, re-layout and env map replicated; device r renders total_spp / n samples of every
+ * pixel with cuRAND subsequences [r * states, (r + 1) * states) (device 0 == the single-GPU stream) into an fp32 sum buffer, ONE
+ * ncclReduce(sum, fp32) of the frame to device 0 (libnccl.so.2 bound at run time, only when n > 1), divide by the sample count,
+ * float4 frame -> HOST memory. `options` as for rt_host_tracer_create (samples_per_launch and kernel_variant unused). */
+typedef struct RtHostMultiTracer RtHostMultiTracer;
+int rt_host_multi_tracer_create(int width, int height, const RtHostTracerOptions* options, const int* devices, int device_count /* 0 = all */,
+                                RtHostMultiTracer** out);
+void rt_host_multi_tracer_destroy(RtHostMultiTracer* tracer);
+int rt_host_multi_tracer_device_count(const RtHostMultiTracer* tracer);
+int rt_host_multi_tracer_set_camera(RtHostMultiTracer* tracer, const float* position3, float angle_x_deg, float angle_y_deg);
+int rt_host_multi_tracer_reseed(RtHostMultiTracer* tracer, uint32_t seed);
+/* Synchronous. timing_ms3 (optional) = slowest device's launches, the reduce, wall clock of the whole call. */
+int rt_host_multi_tracer_render(RtHostMultiTracer* tracer, int total_spp, int spp_per_launch, void* host_pixels, uint64_t host_pitch,
+                                double* timing_ms3);
+unsigned long long rt_host_multi_tracer_ray_count(const RtHostMultiTracer* tracer);
+
 /* headless sink: binary PPM (P6) from RGBA8 rows, top row first */
 int rt_host_write_ppm(const char* path, const uint8_t* rgba8, int width, int height);
 

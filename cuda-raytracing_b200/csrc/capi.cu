@@ -135,7 +135,7 @@ int rt_accel_destroy(RtAccel* a)
     if (!a) return RT_OK;
     {
         std::lock_guard<std::mutex> lock(g_mutex);
-        for (auto it = g_bound.begin(); it != g_bound.end();) it = it->second == a ? g_bound.erase(it) : std::next(it);
+        for (auto it = g_bound.begin(); it != g_bound.end();) it = it->second.accel == a ? g_bound.erase(it) : std::next(it);
     }
     cudaFree((void*)a->view.arena); cudaFree((void*)a->view.shade); cudaFree((void*)a->view.ref_nodes);
     delete a;
@@ -153,15 +153,26 @@ int rt_accel_info(const RtAccel* a, uint64_t* info8)
 int rt_accel_bind(const void* d_nodes_key, RtAccel* a)
 {
     if (!d_nodes_key || !a) return Fail(RT_E_INVALID, "rt_accel_bind: null");
-    std::lock_guard<std::mutex> lock(g_mutex);
-    g_bound[d_nodes_key] = a;
+    RtAccel* replaced = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_mutex);
+        auto it = g_bound.find(d_nodes_key);
+        if (it != g_bound.end() && it->second.owned && it->second.accel != a) replaced = it->second.accel;
+        g_bound[d_nodes_key] = BoundAccel{ a, DeviceBufferId(d_nodes_key), false };
+    }
+    if (replaced) rt_accel_destroy(replaced);  // a library-built re-layout gives way to the caller's
     return RT_OK;
 }
 
 int rt_accel_unbind(const void* d_nodes_key)
 {
-    std::lock_guard<std::mutex> lock(g_mutex);
-    g_bound.erase(d_nodes_key);
+    RtAccel* owned = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_mutex);
+        auto it = g_bound.find(d_nodes_key);
+        if (it != g_bound.end()) { if (it->second.owned) owned = it->second.accel; g_bound.erase(it); }
+    }
+    if (owned) rt_accel_destroy(owned);
     return RT_OK;
 }
 

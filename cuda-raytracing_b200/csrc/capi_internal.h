@@ -12,7 +12,13 @@ namespace rt_internal
 {
     inline thread_local std::string g_error;
     inline std::mutex g_mutex;
-    inline std::map<const void*, RtAccel*> g_bound;  // gpu_bvh_nodes -> accel (raytracing_process lookup)
+    // gpu_bvh_nodes -> re-layout (raytracing_process lookup). buffer_id = CUDA buffer id of the node allocation at bind time (0 = unknown):
+    // a host that freed its arrays and got the same address back has another id, and the binding is dropped instead of used (dropin.cpp).
+    // owned = built by the library itself for an unmodified host (destroyed when replaced, unbound or found stale).
+    struct BoundAccel { RtAccel* accel; uint64_t buffer_id; bool owned; };
+    inline std::map<const void*, BoundAccel> g_bound;
+    uint64_t DeviceBufferId(const void* device_pointer);                       // dropin.cpp
+    int BuildAccelFromDeviceScene(const RtGPUScene* scene, RtAccel** out);     // dropin.cpp
 
     inline int Fail(int code, const std::string& msg) { g_error = msg; return code; }
     inline int CudaFail(cudaError_t e, const char* what) { return Fail(RT_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e)); }

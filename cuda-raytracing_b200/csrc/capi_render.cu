@@ -168,11 +168,38 @@ namespace
         return RT_OK;
     }
 
-    const RtAccel* LookupAccel(const RtGPUScene* scene)
+    // The re-layout for scene->gpu_bvh_nodes: the bound one if it still belongs to that allocation, else one built here from the
+    // GPUScene's own device arrays (an unmodified host never calls rt_accel_bind; csrc/dropin.cpp).
+    int ResolveAccel(const RtGPUScene* scene, const RtAccel** out)
     {
-        std::lock_guard<std::mutex> lock(g_mutex);
-        auto it = g_bound.find(scene->gpu_bvh_nodes);
-        return it == g_bound.end() ? nullptr : it->second;
+        *out = nullptr;
+        const void* key = scene->gpu_bvh_nodes;
+        if (!key) return Fail(RT_E_NOACCEL, "raytracing_process: scene->gpu_bvh_nodes is null");
+        const uint64_t id = DeviceBufferId(key);
+        std::vector<RtAccel*> dead;
+        {
+            std::lock_guard<std::mutex> lock(g_mutex);
+            auto it = g_bound.find(key);
+            if (it != g_bound.end())
+            {
+                if (it->second.buffer_id == 0 || id == 0 || it->second.buffer_id == id) { *out = it->second.accel; return RT_OK; }
+                if (it->second.owned) dead.push_back(it->second.accel);  // same address, another allocation: stale
+                g_bound.erase(it);
+            }
+            // library-built re-layouts whose node arrays are gone (freed, or the address re-used) go with them
+            for (auto jt = g_bound.begin(); jt != g_bound.end();)
+                if (jt->second.owned && jt->second.buffer_id && DeviceBufferId(jt->first) != jt->second.buffer_id) { dead.push_back(jt->second.accel); jt = g_bound.erase(jt); }
+                else ++jt;
+        }
+        for (RtAccel* a : dead) rt_accel_destroy(a);
+        RtAccel* built = nullptr;
+        if (int r = BuildAccelFromDeviceScene(scene, &built)) return r;
+        {
+            std::lock_guard<std::mutex> lock(g_mutex);
+            g_bound[key] = BoundAccel{ built, id, true };
+        }
+        *out = built;
+        return RT_OK;
     }
 }
 
@@ -327,8 +354,8 @@ void raytracing_process(void* surface, void* surface_last_frame, int width, int 
     p.surface = surface; p.surface_last_frame = surface_last_frame; p.width = width; p.height = height; p.pitch = pitch;
     p.frame_index = frame_index; p.samples_per_launch = 5; p.max_bounces = 6; p.blend_mode = 0; p.variant = 0;
     p.scene = scene;
-    p.accel = scene ? LookupAccel(scene) : nullptr;
-    int r = p.accel ? rt_process_ex(&p) : Fail(RT_E_NOACCEL, "raytracing_process: no RtAccel bound for scene->gpu_bvh_nodes (rt_accel_bind)");
+    int r = scene ? ResolveAccel(scene, &p.accel) : Fail(RT_E_INVALID, "raytracing_process: null scene");
+    if (r == RT_OK) r = rt_process_ex(&p);
     if (r != RT_OK) printf("(raytracing_kernel_main) failed to launch error = %d (%s)\n", r, rt_last_error());
 }
 

@@ -26,7 +26,7 @@ extern "C" {
 #define RT_OK 0
 #define RT_E_INVALID (-1)   /* bad argument / inconsistent arrays */
 #define RT_E_CUDA (-2)      /* CUDA runtime error (rt_last_error() has the text) */
-#define RT_E_NOACCEL (-3)   /* raytracing_process() called for a scene with no bound RtAccel */
+#define RT_E_NOACCEL (-3)   /* raytracing_process(): no RtAccel bound AND the scene's device arrays cannot be sized to build one */
 #define RT_E_IO (-4)        /* file missing / malformed */
 #define RT_E_DEPTH (-5)     /* BVH deeper than the traversal stack */
 
@@ -43,8 +43,12 @@ int rt_device_count(void);
 
 /* RayTracing/main_raytracing.cu:202. One progressive frame: 5 spp x <=6 bounces, running-mean blend
  * of `surface_last_frame` into `surface` (alpha=1), default stream, asynchronous. `scene` is a HOST
- * struct whose pointer members are device pointers; its BVH must have been bound with
- * rt_accel_bind() (Scene::Upload does). Errors are printed, as the reference does. */
+ * struct whose pointer members are device pointers. The B200 re-layout of its BVH is the one bound with rt_accel_bind()
+ * (Scene::Upload does); an UNMODIFIED host never binds one, so on the first call for a node array it is built from the scene's own
+ * device arrays (sizes from their allocations and a walk of the tree; ~30 ms for the bunny scene, once) and kept by the library.
+ * A binding is tied to the CUDA buffer id of the node allocation: arrays freed and re-uploaded - even at the same address - get a
+ * new re-layout; a host that OVERWRITES its arrays in place calls rt_accel_unbind(scene->gpu_bvh_nodes). Errors are printed, as
+ * the reference does. */
 void raytracing_process(void* surface, void* surface_last_frame, int width, int height, size_t pitch,
                         int frame_index, RtGPUScene* scene);
 
@@ -74,7 +78,8 @@ int rt_accel_check_host(const RtBVHNode* nodes, uint32_t node_count, const uint3
                         uint32_t fat_leaf_threshold, uint64_t* info4);
 /* info[0..7] = wide nodes, triangle slots, reference leaves, fat leaves, max depth (wide), device bytes lo, hi, reference depth */
 int rt_accel_info(const RtAccel* accel, uint64_t* info8);
-/* associate `accel` with scenes whose gpu_bvh_nodes == d_nodes_key (lookup used by raytracing_process) */
+/* associate `accel` with scenes whose gpu_bvh_nodes == d_nodes_key (lookup used by raytracing_process; valid while that allocation
+ * lives). rt_accel_unbind also releases a re-layout the library built by itself for that key. */
 int rt_accel_bind(const void* d_nodes_key, RtAccel* accel);
 int rt_accel_unbind(const void* d_nodes_key);
 

@@ -181,6 +181,7 @@ class Tracer:
         check(lib().rt_host_tracer_create(ptr(surface), ptr(last_frame_surface), width, height, pitch, C.byref(o), C.byref(h)))
         self.handle = h
         self.scene = Scene(_borrowed=lib().rt_host_tracer_scene(h))
+        self.scene._owner = self  # the borrowed RtHostScene lives inside this tracer: whoever keeps the scene keeps the tracer alive
 
     def process(self):
         check(lib().rt_host_tracer_process(self.handle))

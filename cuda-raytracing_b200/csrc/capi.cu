@@ -81,6 +81,7 @@ int rt_rng_draw(RtRngState* d_states, uint64_t count, uint32_t n, uint32_t* d_ou
 int rt_accel_create(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* face_indices,
                     const RtFace* faces, uint32_t face_count, const RtVertex* vertices, uint32_t vertex_count,
                     uint32_t fat_leaf_threshold, RtAccel** out)
+try
 {
     if (!out) return Fail(RT_E_INVALID, "rt_accel_create: null out");
     *out = nullptr;
@@ -117,10 +118,13 @@ int rt_accel_create(const RtBVHNode* nodes, uint32_t node_count, const uint32_t*
     *out = a;
     return RT_OK;
 }
+catch (const std::exception& e) { return rt_internal::Fail(RT_E_INVALID, std::string("rt_accel_create: ") + e.what()); }
+catch (...) { return rt_internal::Fail(RT_E_INVALID, "rt_accel_create: unknown C++ exception"); }
 
 int rt_accel_check_host(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* face_indices,
                         const RtFace* faces, uint32_t face_count, const RtVertex* vertices, uint32_t vertex_count,
                         uint32_t fat_leaf_threshold, uint64_t* info4)
+try
 {
     AccelHost host;
     if (int r = BuildAccelHost(nodes, node_count, face_indices, faces, face_count, vertices, vertex_count, fat_leaf_threshold, host))
@@ -129,6 +133,8 @@ int rt_accel_check_host(const RtBVHNode* nodes, uint32_t node_count, const uint3
     if (int r = CheckAccelHost(host, nodes, node_count, info4, &why)) return Fail(r, std::string("rt_accel_check_host: ") + why);
     return RT_OK;
 }
+catch (const std::exception& e) { return rt_internal::Fail(RT_E_INVALID, std::string("rt_accel_check_host: ") + e.what()); }
+catch (...) { return rt_internal::Fail(RT_E_INVALID, "rt_accel_check_host: unknown C++ exception"); }
 
 int rt_accel_destroy(RtAccel* a)
 {

@@ -206,6 +206,7 @@ namespace
 extern "C" {
 
 int rt_envmap_create_from_memory(const void* dds_bytes, size_t size, RtEnvMap** out)
+try
 {
     if (!dds_bytes || !out) return Fail(RT_E_INVALID, "rt_envmap_create_from_memory: null");
     DdsImage img; std::string err;
@@ -219,22 +220,30 @@ int rt_envmap_create_from_memory(const void* dds_bytes, size_t size, RtEnvMap** 
     }
     return CreateTexture(static_cast<const uint8_t*>(dds_bytes), img, true, out);  // any other cubemap format CUDA can sample as float4
 }
+catch (const std::exception& e) { return rt_internal::Fail(RT_E_INVALID, std::string("rt_envmap_create_from_memory: ") + e.what()); }
+catch (...) { return rt_internal::Fail(RT_E_INVALID, "rt_envmap_create_from_memory: unknown C++ exception"); }
 
 int rt_texture_create_from_memory(const void* dds_bytes, size_t size, int srgb, RtEnvMap** out)
+try
 {
     if (!dds_bytes || !out) return Fail(RT_E_INVALID, "rt_texture_create_from_memory: null");
     DdsImage img; std::string err;
     if (int r = ParseDds(dds_bytes, size, img, err)) return Fail(r, err);
     return CreateTexture(static_cast<const uint8_t*>(dds_bytes), img, srgb != 0, out);
 }
+catch (const std::exception& e) { return rt_internal::Fail(RT_E_INVALID, std::string("rt_texture_create_from_memory: ") + e.what()); }
+catch (...) { return rt_internal::Fail(RT_E_INVALID, "rt_texture_create_from_memory: unknown C++ exception"); }
 
 int rt_texture_create_from_file(const char* dds_path, int srgb, RtEnvMap** out)
+try
 {
     if (!dds_path || !out) return Fail(RT_E_INVALID, "rt_texture_create_from_file: null");
     std::vector<uint8_t> bytes;
     if (LoadFileBytes(dds_path, bytes)) return Fail(RT_E_IO, std::string("cannot read ") + dds_path);
     return rt_texture_create_from_memory(bytes.data(), bytes.size(), srgb, out);
 }
+catch (const std::exception& e) { return rt_internal::Fail(RT_E_INVALID, std::string("rt_texture_create_from_file: ") + e.what()); }
+catch (...) { return rt_internal::Fail(RT_E_INVALID, "rt_texture_create_from_file: unknown C++ exception"); }
 
 int rt_texture_fetch(const RtEnvMap* tex, int count, const float* d_coords, float lod, float* d_rgba, void* stream)
 {
@@ -246,6 +255,7 @@ int rt_texture_fetch(const RtEnvMap* tex, int count, const float* d_coords, floa
 }
 
 int rt_dds_info(const void* dds_bytes, size_t size, uint64_t* info, int capacity)
+try
 {
     if (!dds_bytes || !info || capacity < 12) return Fail(RT_E_INVALID, "rt_dds_info: bad argument");
     DdsImage img; std::string err;
@@ -260,14 +270,19 @@ int rt_dds_info(const void* dds_bytes, size_t size, uint64_t* info, int capacity
     }
     return n;
 }
+catch (const std::exception& e) { return rt_internal::Fail(RT_E_INVALID, std::string("rt_dds_info: ") + e.what()); }
+catch (...) { return rt_internal::Fail(RT_E_INVALID, "rt_dds_info: unknown C++ exception"); }
 
 int rt_envmap_create_from_file(const char* dds_path, RtEnvMap** out)
+try
 {
     if (!dds_path || !out) return Fail(RT_E_INVALID, "rt_envmap_create_from_file: null");
     std::vector<uint8_t> bytes;
     if (LoadFileBytes(dds_path, bytes)) return Fail(RT_E_IO, std::string("cannot read ") + dds_path);
     return rt_envmap_create_from_memory(bytes.data(), bytes.size(), out);
 }
+catch (const std::exception& e) { return rt_internal::Fail(RT_E_INVALID, std::string("rt_envmap_create_from_file: ") + e.what()); }
+catch (...) { return rt_internal::Fail(RT_E_INVALID, "rt_envmap_create_from_file: unknown C++ exception"); }
 
 uint64_t rt_envmap_texture(const RtEnvMap* env) { return env ? (uint64_t)env->tex : 0; }
 
@@ -281,6 +296,7 @@ int rt_envmap_destroy(RtEnvMap* env)
 }
 
 int rt_dds_read_level0(const char* dds_path, float* out_texels, size_t capacity_floats)
+try
 {
     if (!dds_path) return Fail(RT_E_INVALID, "rt_dds_read_level0: null path");
     std::vector<uint8_t> bytes;
@@ -294,6 +310,8 @@ int rt_dds_read_level0(const char* dds_path, float* out_texels, size_t capacity_
     }
     return (int)dds.size;
 }
+catch (const std::exception& e) { return rt_internal::Fail(RT_E_INVALID, std::string("rt_dds_read_level0: ") + e.what()); }
+catch (...) { return rt_internal::Fail(RT_E_INVALID, "rt_dds_read_level0: unknown C++ exception"); }
 
 // ---- closest-hit queries --------------------------------------------------------------------
 int rt_trace_primary(const RtAccel* accel, const RtGPUScene* scene, int width, int height, int with_spheres,

@@ -56,6 +56,17 @@ int ParseDdsCubemap(const void* bytes, size_t size, DdsCubemap& out, std::string
 
     out.size = h.width;
     out.mip_count = h.mipMapCount ? h.mipMapCount : 1;
+    // nothing is allocated on the header's word alone: a full chain has floor(log2(size)) + 1 levels (and at most 16 here, sizes up
+    // to 16384 like ParseDds), and the pixel data the header promises must actually be in the file
+    if (h.width > 16384) { error = "DDS: cubemap face larger than 16384"; return RT_E_IO; }
+    uint32_t full_chain = 1;
+    while ((h.width >> full_chain) != 0 && full_chain < 16) full_chain++;
+    if (out.mip_count > full_chain) { error = "DDS: more mip levels than the face size allows"; return RT_E_IO; }
+    {
+        size_t need = 0;
+        for (uint32_t m = 0; m < out.mip_count; m++) { const size_t w = (out.size >> m) ? (out.size >> m) : 1; need += 6 * w * w * 16; }
+        if (need > size - offset) { error = "DDS: truncated pixel data"; return RT_E_IO; }
+    }
     out.levels.assign(out.mip_count, {});
     for (uint32_t m = 0; m < out.mip_count; m++)
     {

@@ -118,3 +118,23 @@ def test_rejections_of_container_rules(rt, ref):
     for name, data in cases.items():
         assert our_info(rt, data)[0] < 0, name
         assert ref.dds_info(data)[0] < 0, name + " (reference accepts it)"
+
+
+def test_malformed_cubemap_headers_fail_before_allocating(rt, tmp_path):
+    """the RGBA32F cubemap reader must not trust mipMapCount / width before it has checked the file size (a header
+    that promises 2^31 mips or a 16384^2 x 6 chain used to allocate tens of GB and throw across the C ABI)."""
+    import struct
+    texels = np.zeros((6, 4, 4, 4), np.float32)
+    path = str(tmp_path / "ok.dds")
+    util.write_dds_cubemap(path, texels)
+    good = bytearray(open(path, "rb").read())
+    assert rt.lib().rt_dds_read_level0(path.encode(), None, 0) == 4
+    for name, offset, value in (("mips", 4 + 24, 0x7FFFFFFF), ("mips33", 4 + 24, 33), ("width", 4 + 12, 16384), ("huge", 4 + 12, 1 << 20)):
+        bad = bytearray(good)
+        struct.pack_into("<I", bad, offset, value)
+        if name in ("width", "huge"):
+            struct.pack_into("<I", bad, 4 + 8, value)  # height too (faces must be square)
+        p = str(tmp_path / (name + ".dds"))
+        open(p, "wb").write(bad)
+        assert rt.lib().rt_dds_read_level0(p.encode(), None, 0) < 0, name
+        assert b"DDS" in rt.lib().rt_last_error()

@@ -18,7 +18,7 @@ LIB_DIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIB_DIR, "libb200rt.so")
 
 SOURCES = [
-    "csrc/kernels.cu", "csrc/pathtrace.cu", "csrc/pathtrace_regroup.cu", "csrc/capi.cu", "csrc/capi_render.cu",
+    "csrc/kernels.cu", "csrc/pathtrace.cu", "csrc/pathtrace_regroup.cu", "csrc/pathtrace_wavefront.cu", "csrc/capi.cu", "csrc/capi_render.cu",
     "csrc/accel_build.cpp", "csrc/dropin.cpp", "csrc/dds.cpp", "csrc/rng_host.cpp",
     "host/Math.cpp", "host/BVH.cpp", "host/MeshLoader.cpp", "host/Subdivide.cpp", "host/Scene.cpp",
     "host/SceneSetup.cpp", "host/SceneUpload.cpp", "host/RayTracing.cpp", "host/MultiGPU.cpp", "host/host_capi.cpp",

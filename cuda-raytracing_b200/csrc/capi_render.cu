@@ -343,7 +343,9 @@ int rt_count_reference_work(const RtAccel* accel, const RtGPUScene* scene, int w
 // ---- path tracing ---------------------------------------------------------------------------
 uint64_t rt_process_workspace_bytes(int width, int height, int variant)
 {
-    return variant == 0 && width > 0 && height > 0 ? PathTraceWorkspaceBytes(width, height) : 0;
+    if (width <= 0 || height <= 0) return 0;
+    if (variant == 10) return PathTraceWavefrontWorkspaceBytes(width, height);
+    return variant == 0 || (variant >= 4 && variant <= 9) ? PathTraceWorkspaceBytes(width, height) : 0;
 }
 
 int rt_process_ex(const RtProcessParams* p)
@@ -353,7 +355,14 @@ int rt_process_ex(const RtProcessParams* p)
     if (p->samples_per_launch <= 0 || p->max_bounces <= 0) return Fail(RT_E_INVALID, "rt_process_ex: spp and bounces must be positive");
     if (p->pitch < (uint64_t)p->width * 16) return Fail(RT_E_INVALID, "rt_process_ex: pitch smaller than a row");
     if (!p->scene->rng_state) return Fail(RT_E_INVALID, "rt_process_ex: scene has no rng_state");
-    if (p->variant < 0 || p->variant > 3) return Fail(RT_E_INVALID, "rt_process_ex: unknown variant");
+    if (p->variant < 0 || p->variant > 10) return Fail(RT_E_INVALID, "rt_process_ex: unknown variant");
+    if (p->variant == 10)
+    {
+        if (!p->workspace || p->workspace_bytes < PathTraceWavefrontWorkspaceBytes(p->width, p->height) || (int64_t)p->samples_per_launch * p->max_bounces > 4096)
+            return Fail(RT_E_INVALID, "rt_process_ex: the wavefront variant needs a workspace of rt_process_workspace_bytes(width, height, 10) and spp x bounces <= 4096");
+        RT_CUDA(LaunchPathTraceWavefront(p->accel->view, MakeSceneView(p->scene), *p, (cudaStream_t)p->stream));
+        return RT_OK;
+    }
     if (p->write_last_frame && !p->surface_last_frame) return Fail(RT_E_INVALID, "rt_process_ex: write_last_frame needs surface_last_frame");
     if (p->variant == 1)
     {

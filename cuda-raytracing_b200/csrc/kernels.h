@@ -41,3 +41,6 @@ cudaError_t LaunchAmbientOcclusion(const AccelView& accel, const SceneView& scen
 cudaError_t LaunchTonemap(const void* surface, int width, int height, uint64_t pitch, float divide_by, uint8_t* d_rgba8,
                           cudaStream_t stream);
 cudaError_t LaunchResolveSum(const void* sum, void* out, int width, int height, uint64_t pitch_in, uint64_t pitch_out, cudaStream_t stream);
+// variant 10: queue-based wavefront (pathtrace_wavefront.cu); workspace = PathTraceWavefrontWorkspaceBytes, any contents
+cudaError_t LaunchPathTraceWavefront(const AccelView& accel, const SceneView& scene, const RtProcessParams& p, cudaStream_t stream);
+uint64_t PathTraceWavefrontWorkspaceBytes(int width, int height);

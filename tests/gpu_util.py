@@ -71,10 +71,15 @@ class DeviceScene:
         return ids.cpu().numpy().view(np.uint32)[:n], ts.cpu().numpy()[:n]
 
     def process(self, frame_index, spp=5, bounces=6, blend_mode=0, variant=0, write_last=0, surface=None, last=None, ordered=True):
-        from cuda_raytracing_b200.api import process_ex
+        from cuda_raytracing_b200.api import process_ex, process_workspace_bytes
+        ws = self.workspace if ordered else None
+        if variant == 10:  # queue-based wavefront: path states + ray queues live in its (much larger) workspace
+            if getattr(self, "wavefront_workspace", None) is None:
+                self.wavefront_workspace = self.torch.empty(process_workspace_bytes(self.width, self.height, 10), dtype=self.torch.uint8, device=self.device)
+            ws = self.wavefront_workspace
         process_ex(self.surface if surface is None else surface, self.last if last is None else last, self.width, self.height,
                    self.pitch, frame_index, self.gpu, self.accel, spp=spp, bounces=bounces, blend_mode=blend_mode, variant=variant,
-                   write_last=write_last, ray_counter=self.counter, workspace=self.workspace if ordered else None)
+                   write_last=write_last, ray_counter=self.counter, workspace=ws)
 
     def rays(self):
         self.torch.cuda.synchronize()

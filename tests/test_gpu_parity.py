@@ -460,6 +460,29 @@ def test_regroup_variant_bit_identical_to_megakernel(rt, torch_cuda, size):
     assert t.equal(sa, sb)
 
 
+@pytest.mark.parametrize("variant", [4, 6, 8, 10])
+def test_batched_and_wavefront_variants_bit_identical_to_megakernel(rt, torch_cuda, variant):
+    """variants 4-9 (batched megakernel: K pixels per lane, one traversal loop over a lane's K rays) and variant 10 (queue-based
+    wavefront: path state in HBM, ballot / prefix-sum compaction into camera + octant queues between stages, north-star item 3) run
+    the same per-pixel sequence of draws and fp32 operations as variant 0: surfaces, RNG states and ray counts are identical.
+    Frame sizes that do not fill the tiles; running-mean and sum blend."""
+    t = torch_cuda
+    for (W, H) in ((200, 120), (37, 23)):
+        a = gpu_util.DeviceScene(rt, t, W, H, "poseB", seed=21, env=True)
+        b = gpu_util.DeviceScene(rt, t, W, H, "poseB", seed=21, env=True)
+        for f in range(2):
+            a.process(f, spp=7, bounces=4, variant=0, write_last=1)
+            b.process(f, spp=7, bounces=4, variant=variant, write_last=1)
+        t.cuda.synchronize()
+        assert t.equal(a.surface, b.surface) and t.equal(a.last, b.last)
+        assert t.equal(a.rng, b.rng)
+        assert a.rays() == b.rays()
+        sa = t.zeros_like(a.surface); sb = t.zeros_like(a.surface)
+        a.process(0, spp=3, bounces=6, blend_mode=1, variant=0, surface=sa)
+        b.process(0, spp=3, bounces=6, blend_mode=1, variant=variant, surface=sb)
+        assert t.equal(sa, sb)
+
+
 def test_converged_image_rmse_vs_reference_at_1024spp(rt, torch_cuda):
     """BASELINE.json's image bar: the path-traced image at ~1024 spp has RMSE <= 1 % of the reference's converged image.
     Reference = the pinned plain-C port of raytracing_kernel_main (bit-identical to oracle/_ref) run live on the box's host cores:

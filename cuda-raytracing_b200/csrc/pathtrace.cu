@@ -203,18 +203,29 @@ __global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks) pathtrace_batched_ker
 // the same frame takes 56.0 / 59.3 / 60.9 ms with tile rows scheduled bottom-up / top-down / strided). With a workspace, every
 // launch records each tile's cost and the next launch schedules tiles heaviest-first (longest-processing-time-first list
 // scheduling). Pixels are independent, so the image and the RNG streams do not depend on the order.
-// Workspace (uint32): [0] width, [1] height, [2] tile count, [3] reserved | order[n] | cost[n]; zero-filled = fresh.
+// A history is only as good as the camera that made it: when the camera moved since the costs were measured, ordering by the
+// stale costs is WORSE than grid order (profiles/r02j_moving_camera.json: 47.5 vs 44.8 ms at 2 degrees per frame - the tiles that
+// just became expensive sit anywhere in the order). The workspace therefore remembers a hash of the camera; after a move the costs
+// are first DILATED (maximum over a 13 x 25-tile = 208 x 200-pixel neighbourhood: whatever was expensive is probably still
+// expensive nearby), so the newly expensive tiles are scheduled early too: 42.2 ms (2 degrees per frame) and 39.4 ms (10 degrees)
+// against 45.0 / 41.5 ms in grid order and 47.6 / 42.5 ms with the stale order; a static camera keeps its 44.9 (grid: 47.5).
+// Workspace (uint32): [0] width, [1] height, [2] tile count, [3] launches with a history, [4] camera hash, [5..7] reserved
+//                     | order[n] | cost[n] | scratch[n]; zero-filled = fresh.
 // ------------------------------------------------------------------------------------------------
-#define RT_TILE_HDR 4u
+#define RT_TILE_HDR 8u
 #define RT_TILE_BUCKETS 256
+#ifndef RT_TILE_DILATE_X
+#define RT_TILE_DILATE_X 6
+#define RT_TILE_DILATE_Y 12
+#endif
 
 // one CTA: counting sort of the tiles into RT_TILE_BUCKETS cost classes, heaviest class first (order inside a class is arbitrary)
-__global__ void __launch_bounds__(1024) tile_order_kernel(uint32_t* ws, uint32_t width, uint32_t height, uint32_t n)
+__global__ void __launch_bounds__(1024) tile_order_kernel(uint32_t* ws, uint32_t width, uint32_t height, uint32_t n, uint32_t tiles_x, uint32_t camera_hash)
 {
     __shared__ uint32_t hist[RT_TILE_BUCKETS];
-    __shared__ uint32_t s_max, s_fresh;
-    uint32_t* order = ws + RT_TILE_HDR; uint32_t* cost = order + n;
-    if (threadIdx.x == 0) { s_max = 0; s_fresh = ws[0] != width || ws[1] != height || ws[2] != n; }
+    __shared__ uint32_t s_max, s_fresh, s_moved;
+    uint32_t* order = ws + RT_TILE_HDR; uint32_t* cost = order + n; uint32_t* scratch = cost + n;
+    if (threadIdx.x == 0) { s_max = 0; s_fresh = ws[0] != width || ws[1] != height || ws[2] != n; s_moved = ws[4] != camera_hash; }
     for (uint32_t i = threadIdx.x; i < RT_TILE_BUCKETS; i += blockDim.x) hist[i] = 0;
     __syncthreads();
     const bool fresh = s_fresh != 0u;
@@ -229,8 +240,28 @@ __global__ void __launch_bounds__(1024) tile_order_kernel(uint32_t* ws, uint32_t
     if (fresh || mx == 0)
     {   // no measurement yet (or another frame size): grid order
         for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) { order[i] = i; cost[i] = 0; }
-        if (threadIdx.x == 0) { ws[0] = width; ws[1] = height; ws[2] = n; ws[3] = 0; }
+        if (threadIdx.x == 0) { ws[0] = width; ws[1] = height; ws[2] = n; ws[3] = 0; ws[4] = camera_hash; }
         return;
+    }
+    if (s_moved != 0u && (RT_TILE_DILATE_X || RT_TILE_DILATE_Y))
+    {   // separable maximum filter: rows into scratch, columns back into cost (the maximum over all tiles, mx, is unchanged)
+        const uint32_t tiles_y = n / tiles_x;
+        for (uint32_t i = threadIdx.x; i < n; i += blockDim.x)
+        {
+            const uint32_t tx = i % tiles_x, row = i - tx;
+            uint32_t m = 0;
+            for (uint32_t x = tx > RT_TILE_DILATE_X ? tx - RT_TILE_DILATE_X : 0; x <= min(tx + RT_TILE_DILATE_X, tiles_x - 1); x++) m = max(m, cost[row + x]);
+            scratch[i] = m;
+        }
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < n; i += blockDim.x)
+        {
+            const uint32_t tx = i % tiles_x, ty = i / tiles_x;
+            uint32_t m = 0;
+            for (uint32_t y = ty > RT_TILE_DILATE_Y ? ty - RT_TILE_DILATE_Y : 0; y <= min(ty + RT_TILE_DILATE_Y, tiles_y - 1); y++) m = max(m, scratch[y * tiles_x + tx]);
+            cost[i] = m;
+        }
+        __syncthreads();
     }
     const float scale = (float)(RT_TILE_BUCKETS - 1) / (float)mx;
     for (uint32_t i = threadIdx.x; i < n; i += blockDim.x)
@@ -249,13 +280,13 @@ __global__ void __launch_bounds__(1024) tile_order_kernel(uint32_t* ws, uint32_t
     }
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) cost[i] = 0;  // this launch's atomicMax starts from zero
-    if (threadIdx.x == 0) ws[3]++;
+    if (threadIdx.x == 0) { ws[3]++; ws[4] = camera_hash; }
 }
 
 uint64_t PathTraceWorkspaceBytes(int width, int height)
 {
     const uint64_t n = (uint64_t)((width + 15) / 16) * (uint64_t)((height + RT_PT_BLOCK / 16 - 1) / (RT_PT_BLOCK / 16));
-    return (RT_TILE_HDR + 2 * n) * sizeof(uint32_t);
+    return (RT_TILE_HDR + 3 * n) * sizeof(uint32_t);
 }
 
 cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, const RtProcessParams& p, cudaStream_t stream)
@@ -276,7 +307,10 @@ cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, cons
     {
         const uint32_t n = grid.x * grid.y;
         uint32_t* ws = (uint32_t*)p.workspace;
-        tile_order_kernel<<<1, 1024, 0, stream>>>(ws, (uint32_t)p.width, (uint32_t)p.height, n);
+        uint32_t camera_hash = 2166136261u;  // FNV-1a over the 60 bytes of the GPUCamera
+        for (size_t k = 0; k < sizeof(RtCamera); k++) camera_hash = (camera_hash ^ reinterpret_cast<const unsigned char*>(&scene.camera)[k]) * 16777619u;
+        if (camera_hash == 0) camera_hash = 1;
+        tile_order_kernel<<<1, 1024, 0, stream>>>(ws, (uint32_t)p.width, (uint32_t)p.height, n, grid.x, camera_hash);
         P.tile_order = ws + RT_TILE_HDR; P.tile_cost = ws + RT_TILE_HDR + n;
         grid = dim3(n, 1);
     }
@@ -361,9 +395,9 @@ cudaError_t LaunchAmbientOcclusion(const AccelView& accel, const SceneView& scen
 // ------------------------------------------------------------------------------------------------
 // rt_process_ex_static_scratch: rt_process_ex for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
 // serving loops, harnesses that forbid it). No counterpart in the reference.
-// The cost-ordered tile schedule's scratch (header + tile order + tile cost, RT_TILE_HDR + 2 n words) lives in a file-scope
+// The cost-ordered tile schedule's scratch (header + tile order + tile cost + filter scratch, RT_TILE_HDR + 3 n words) lives in a file-scope
 // device array instead of a caller-allocated workspace: RT_STATIC_SCRATCH_BYTES = 1 MiB per GPU that loads the library, held
-// until exit - room for 131 070 tiles of 16 x 8 pixels = 16.7 M pixels (a 4K frame has 64 800 tiles).
+// until exit - room for 87 378 tiles of 16 x 8 pixels = 11.1 M pixels (a 4K frame has 64 800 tiles).
 // In HOST code the array's name is a host-side stand-in, not a device address: its device address is taken once per device with
 // cudaGetSymbolAddress while that device is current, and that pointer is what the launch receives.
 // ------------------------------------------------------------------------------------------------
@@ -410,7 +444,7 @@ extern "C" int rt_process_ex_static_scratch(const RtProcessParams* params)
     const uint64_t need = PathTraceWorkspaceBytes(params->width, params->height);
     if (need > RT_STATIC_SCRATCH_BYTES)
         return Fail(RT_E_INVALID, "rt_process_ex_static_scratch: frame needs " + std::to_string(need) + " bytes of tile scratch, the static array holds " +
-                                      std::to_string(RT_STATIC_SCRATCH_BYTES) + " (131070 tiles of 16x8 pixels); use rt_process_ex with a caller-owned workspace");
+                                      std::to_string(RT_STATIC_SCRATCH_BYTES) + " (87378 tiles of 16x8 pixels); use rt_process_ex with a caller-owned workspace");
     void* scratch = nullptr;
     if (int r = StaticScratch(&scratch)) return r;
     // The array is shared by every call on this device and keeps the last call's contents. What must start at zero does: the header

@@ -155,7 +155,7 @@ uint64_t rt_process_workspace_bytes(int width, int height, int variant);
  * cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it): the tile-schedule scratch that
  * `workspace` would name lives in a file-scope device array of rt_process_static_scratch_bytes() = 1 MiB per GPU that loads the
  * library (held until exit), so `workspace` / `workspace_bytes` of `params` are ignored and the call allocates nothing, on the host
- * side of CUDA or the device. Limit: frames of at most 131 070 tiles of 16 x 8 pixels (16.7 M pixels; 4K = 64 800 tiles) -
+ * side of CUDA or the device. Limit: frames of at most 87 378 tiles of 16 x 8 pixels (11.1 M pixels; 4K = 64 800 tiles) -
  * larger frames return RT_E_INVALID with the sizes in rt_last_error(). Same image, RNG states and ray count as rt_process_ex
  * (the schedule only orders independent pixels). Every call on a device shares the array: a call with frame_index == 0 drops the
  * schedule history, later frames reuse the previous launch's measured tile costs; calls that OVERLAP on one GPU (two streams,

@@ -291,12 +291,32 @@ def test_cost_ordered_tile_schedule_does_not_change_the_frame(rt, torch_cuda):
     ws = a.workspace.view(torch_cuda.int32).cpu().numpy().view(np.uint32)
     n = ((W + 15) // 16) * ((H + 7) // 8)
     assert tuple(ws[:3]) == (W, H, n) and ws[3] == 2  # two launches found a cost history
-    order, cost = ws[4:4 + n], ws[4 + n:4 + 2 * n]
+    order, cost = ws[8:8 + n], ws[8 + n:8 + 2 * n]
     assert np.array_equal(np.sort(order), np.arange(n, dtype=np.uint32))
     assert (cost > 0).all()  # every tile ran and reported
     prev = b.workspace  # the other scene's workspace was never used
     assert int(prev.view(torch_cuda.int32).abs().sum().item()) == 0
-    assert rt.lib().rt_process_workspace_bytes(W, H, 0) == (4 + 2 * n) * 4
+    assert rt.lib().rt_process_workspace_bytes(W, H, 0) == (8 + 3 * n) * 4
+
+
+def test_tile_schedule_under_a_moving_camera_does_not_change_the_frames(rt, torch_cuda):
+    """After a camera move the schedule dilates the previous pose's tile costs (pathtrace.cu tile_order_kernel): still only an order
+    of independent pixels - frames and RNG states equal the unordered run's at every pose, the workspace tracks the camera."""
+    W, H = 200, 120
+    a = gpu_util.DeviceScene(rt, torch_cuda, W, H, "poseB", seed=5, env=True)
+    b = gpu_util.DeviceScene(rt, torch_cuda, W, H, "poseB", seed=5, env=True)
+    hashes = set()
+    for k, pose in enumerate((util.POSES["poseB"], ((30.0, -1.0, 3.0), 1.0, 184.0), ((27.0, 0.0, 5.0), 3.0, 195.0), ((27.0, 0.0, 5.0), 3.0, 195.0))):
+        a.set_pose(pose); b.set_pose(pose)
+        a.process(0, spp=4, bounces=4, write_last=1, ordered=True)
+        b.process(0, spp=4, bounces=4, write_last=1, ordered=False)
+        torch_cuda.cuda.synchronize()
+        assert torch_cuda.equal(a.surface, b.surface) and torch_cuda.equal(a.rng, b.rng), k
+        ws = a.workspace.view(torch_cuda.int32).cpu().numpy().view(np.uint32)
+        n = ((W + 15) // 16) * ((H + 7) // 8)
+        assert np.array_equal(np.sort(ws[8:8 + n]), np.arange(n, dtype=np.uint32))  # still a permutation of the tiles
+        hashes.add(int(ws[4]))
+    assert len(hashes) == 3  # three distinct cameras seen, the repeated pose kept its hash
 
 
 def test_sample_split_is_stream_continuous(rt, torch_cuda):

@@ -56,7 +56,7 @@ def test_static_scratch_entry_matches_rt_process_ex_on_two_calls_in_a_row(rt, to
 
 def test_static_scratch_entry_rejects_what_it_cannot_hold(rt, torch_cuda):
     d = gpu_util.DeviceScene(rt, torch_cuda, 64, 48, "poseB", seed=1, env=False)
-    # 16384 x 16384 = 2 097 152 tiles: beyond the 1 MiB array (131 070 tiles); rejected before anything is launched or touched
+    # 16384 x 16384 = 2 097 152 tiles: beyond the 1 MiB array (87 378 tiles); rejected before anything is launched or touched
     assert process_static(rt, d, 0, 1, 1, width=16384, height=16384) == -1
     msg = rt.lib().rt_last_error().decode()
     assert "static array holds 1048576" in msg and "rt_process_ex" in msg

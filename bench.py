@@ -200,13 +200,13 @@ def measured_peaks():
 
 
 def csrc_hash():
-    """sha1 over the device sources: profiles/traffic.json records it, so a stale ncu capture is never applied to another kernel."""
+    """sha1 over the sources the megakernel is compiled from: profiles/traffic.json records it, so a stale ncu capture is never
+    applied to another kernel."""
     import hashlib
     h = hashlib.sha1()
     d = os.path.join(ROOT, "cuda-raytracing_b200", "csrc")
-    for name in sorted(os.listdir(d)):
-        if name.endswith((".cu", ".cuh", ".h")):
-            h.update(name.encode()); h.update(open(os.path.join(d, name), "rb").read())
+    for name in ("accel.h", "kernels.h", "pathtrace.cu", "pathtrace_common.cuh", "rng.cuh", "shade.cuh", "traverse.cuh"):  # what the megakernel is compiled from
+        h.update(name.encode()); h.update(open(os.path.join(d, name), "rb").read())
     return h.hexdigest()[:16]
 
 

@@ -345,7 +345,7 @@ uint64_t rt_process_workspace_bytes(int width, int height, int variant)
 {
     if (width <= 0 || height <= 0) return 0;
     if (variant == 10) return PathTraceWavefrontWorkspaceBytes(width, height);
-    return variant == 0 || (variant >= 4 && variant <= 9) ? PathTraceWorkspaceBytes(width, height) : 0;
+    return variant == 0 ? PathTraceWorkspaceBytes(width, height) : 0;
 }
 
 int rt_process_ex(const RtProcessParams* p)
@@ -355,7 +355,7 @@ int rt_process_ex(const RtProcessParams* p)
     if (p->samples_per_launch <= 0 || p->max_bounces <= 0) return Fail(RT_E_INVALID, "rt_process_ex: spp and bounces must be positive");
     if (p->pitch < (uint64_t)p->width * 16) return Fail(RT_E_INVALID, "rt_process_ex: pitch smaller than a row");
     if (!p->scene->rng_state) return Fail(RT_E_INVALID, "rt_process_ex: scene has no rng_state");
-    if (p->variant < 0 || p->variant > 10) return Fail(RT_E_INVALID, "rt_process_ex: unknown variant");
+    if (p->variant < 0 || p->variant > 10 || (p->variant >= 4 && p->variant <= 9)) return Fail(RT_E_INVALID, "rt_process_ex: unknown variant");
     if (p->variant == 10)
     {
         if (!p->workspace || p->workspace_bytes < PathTraceWavefrontWorkspaceBytes(p->width, p->height) || (int64_t)p->samples_per_launch * p->max_bounces > 4096)

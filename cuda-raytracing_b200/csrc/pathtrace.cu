@@ -92,112 +92,6 @@ __global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks * (256 / RT_PT_BLOCK))
 }
 
 // ------------------------------------------------------------------------------------------------
-// Batched megakernel: one lane owns K pixels (K independent paths) and every round traces ONE ray of each of them in a single
-// traversal loop (trace_wide_batch, traverse.cuh): the round lasts as long as the slowest lane's SUM of K rays instead of its one
-// ray, so fewer lane-iterations idle behind the slowest lane. Ray set-up (camera ray / normalise / spheres) and shading of all K
-// paths run outside the loop at the warp's full width. Per pixel the sequence of draws and fp32 operations is unchanged:
-// image, RNG states and ray count are bit-identical to pathtrace_megakernel<0>.
-// CTA = 16 x (8 K) pixels; lane's pixel j = its 8 x 4 warp footprint moved down by 8 j rows.
-// ------------------------------------------------------------------------------------------------
-struct BatchedPath
-{
-    PathState ps;
-    Xorwow rng;
-    Vec3 sum;
-    int sample, bounce;
-    int x, y;
-    bool fresh, active;
-};
-
-template <int K, int kMinBlocks>
-__global__ void __launch_bounds__(RT_PT_BLOCK, kMinBlocks) pathtrace_batched_kernel(AccelView A, SceneView S, FrameParams P)
-{
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    constexpr int kTileH = (RT_PT_BLOCK / 16) * K;
-    unsigned bx = blockIdx.x, by = blockIdx.y;
-    unsigned tile = 0;
-    long long t_start = 0;
-    if (P.tile_order)
-    {
-        const unsigned tiles_x = ((unsigned)P.width + 15u) >> 4;
-        tile = __ldg(P.tile_order + blockIdx.x);
-        bx = tile % tiles_x; by = tile / tiles_x;
-        t_start = clock64();
-    }
-    constexpr int kWarpsX = 16 / RT_PT_WARP_W, kWarpH = 32 / RT_PT_WARP_W;
-    BatchedPath path[K];
-    RayRecord rec[K];
-    unsigned rays = 0;
-#pragma unroll 1
-    for (int j = 0; j < K; j++)
-    {
-        BatchedPath& p = path[j];
-        p.x = bx * 16 + (warp % kWarpsX) * RT_PT_WARP_W + (lane % RT_PT_WARP_W);
-        p.y = by * kTileH + j * (RT_PT_BLOCK / 16) + (warp / kWarpsX) * kWarpH + (lane / RT_PT_WARP_W);
-        p.active = p.x < P.width && p.y < P.height;
-        p.sum = mk3(0, 0, 0); p.sample = p.active ? 0 : P.spp; p.bounce = 0; p.fresh = true;
-        if (p.active) p.rng.load(S.rng_state + (size_t)p.y * P.width + p.x);  // GPUScene::GetRNGForPixel, GPUScene.h:95
-    }
-    for (;;)
-    {
-        bool any = false;
-#pragma unroll 1
-        for (int j = 0; j < K; j++)
-        {   // ray set-up of every unfinished path, at the warp's full width
-            BatchedPath& p = path[j];
-            RayRecord& r = rec[j];
-            r.t0 = -1.0f;
-            if (p.sample >= P.spp) continue;
-            any = true;
-            if (p.fresh)
-            {   // main_raytracing.cu:190-191; jitter draws x first, then y
-                const float jx = p.rng.uniform(), jy = p.rng.uniform();
-                const float u = ((float)p.x + jx) / (float)P.width, v = ((float)p.y + jy) / (float)P.height;
-                camera_ray_pt(S.camera, u, v, p.ps.o, p.ps.d);
-                p.ps.throughput = mk3(1, 1, 1); p.ps.radiance = mk3(0, 0, 0);
-                p.bounce = 0; p.fresh = false;
-            }
-            r.o = p.ps.o; r.d = p.ps.d; r.nd = normalize3(p.ps.d);
-            HitRecord h; h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
-            sphere_tests(S.spheres, S.sphere_count, r.o, r.nd, h);
-            r.t0 = h.t; r.t = h.t; r.id = h.id; r.slot = h.slot; r.bu = 0; r.bv = 0;
-        }
-        if (!any) break;
-        trace_wide_batch<false, K>(A, rec);
-#pragma unroll 1
-        for (int j = 0; j < K; j++)
-        {   // deferred leaf-box check + shading of every traced ray
-            if (rec[j].t0 < 0.0f) continue;
-            BatchedPath& p = path[j];
-            const HitRecord h = finish_batched_ray<false>(A, S.spheres, S.sphere_count, rec[j]);
-            rays++;
-            bool alive;
-            if (h.id != RT_MISS_ID) alive = shade_hit(A, S, h, p.ps, p.rng) && (++p.bounce < P.max_bounces);
-            else { if (S.env_tex) shade_miss(S, P.consts, p.ps); alive = false; }
-            if (!alive) { p.sum = p.sum + p.ps.radiance; p.sample++; p.fresh = true; }
-        }
-    }
-#pragma unroll 1
-    for (int j = 0; j < K; j++)
-    {
-        BatchedPath& p = path[j];
-        if (!p.active) continue;
-        p.rng.store(S.rng_state + (size_t)p.y * P.width + p.x);
-        write_pixel(P, p.x, p.y, p.sum);
-    }
-    if (P.tile_order && lane == 0)
-    {
-        const unsigned long long c = (unsigned long long)(clock64() - t_start) >> 4;
-        atomicMax(P.tile_cost + tile, (uint32_t)(c > 0xFFFFFFFFull ? 0xFFFFFFFFull : c));
-    }
-    if (P.ray_counter)
-    {
-        for (int o = 16; o; o >>= 1) rays += __shfl_xor_sync(0xffffffffu, rays, o);
-        if (lane == 0 && rays) atomicAdd(P.ray_counter, (unsigned long long)rays);
-    }
-}
-
-// ------------------------------------------------------------------------------------------------
 // Cost-ordered tile scheduling. Per-tile cost varies ~10x (sky vs bunny silhouette) and the hardware hands out CTAs in grid order,
 // so in raster order the launch ends whenever the last expensive tiles happen to finish while most SMs already idle (measured:
 // the same frame takes 56.0 / 59.3 / 60.9 ms with tile rows scheduled bottom-up / top-down / strided). With a workspace, every
@@ -297,13 +191,11 @@ cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, cons
     P.spp = p.samples_per_launch; P.max_bounces = p.max_bounces; P.blend_mode = p.blend_mode; P.write_last = p.write_last_frame;
     P.ray_counter = p.d_ray_counter; P.work_counters = p.d_work_counters;
     P.consts = MakePathConsts();
-    // variants 4..9: the batched kernel with K = 2, 3, 4 pixels per lane at 10 CTAs per SM (48 registers), then the same at 8 (64)
-    const int batch_k = p.variant >= 4 && p.variant <= 9 ? 2 + (p.variant - 4) % 3 : 1;
-    const int tile_h = (RT_PT_BLOCK / 16) * batch_k;
+    const int tile_h = RT_PT_BLOCK / 16;
     dim3 grid((p.width + 15) / 16, (p.height + tile_h - 1) / tile_h), block(RT_PT_BLOCK);
     P.tile_order = nullptr; P.tile_cost = nullptr;
     // a workspace switches the cost-ordered schedule on (p.workspace == nullptr: grid order, also what the reference-named entry uses)
-    if ((p.variant == 0 || batch_k > 1) && p.workspace && p.workspace_bytes >= PathTraceWorkspaceBytes(p.width, p.height))
+    if (p.variant == 0 && p.workspace && p.workspace_bytes >= PathTraceWorkspaceBytes(p.width, p.height))
     {
         const uint32_t n = grid.x * grid.y;
         uint32_t* ws = (uint32_t*)p.workspace;
@@ -314,13 +206,7 @@ cudaError_t LaunchPathTrace(const AccelView& accel, const SceneView& scene, cons
         P.tile_order = ws + RT_TILE_HDR; P.tile_cost = ws + RT_TILE_HDR + n;
         grid = dim3(n, 1);
     }
-    if (p.variant == 4) pathtrace_batched_kernel<2, 10><<<grid, block, 0, stream>>>(accel, scene, P);
-    else if (p.variant == 5) pathtrace_batched_kernel<3, 10><<<grid, block, 0, stream>>>(accel, scene, P);
-    else if (p.variant == 6) pathtrace_batched_kernel<4, 10><<<grid, block, 0, stream>>>(accel, scene, P);
-    else if (p.variant == 7) pathtrace_batched_kernel<2, 8><<<grid, block, 0, stream>>>(accel, scene, P);
-    else if (p.variant == 8) pathtrace_batched_kernel<3, 8><<<grid, block, 0, stream>>>(accel, scene, P);
-    else if (p.variant == 9) pathtrace_batched_kernel<4, 8><<<grid, block, 0, stream>>>(accel, scene, P);
-    else if (p.variant == 2) pathtrace_megakernel<2, 3><<<grid, block, 0, stream>>>(accel, scene, P);
+    if (p.variant == 2) pathtrace_megakernel<2, 3><<<grid, block, 0, stream>>>(accel, scene, P);
     else if (p.variant == 3) pathtrace_megakernel<3, 5><<<grid, block, 0, stream>>>(accel, scene, P);
     else pathtrace_megakernel<0, 5><<<grid, block, 0, stream>>>(accel, scene, P);  // 5 x 256 threads per SM (48 registers): 3 / 4 / 5 / 6 = 57.4 / 55.3 / 52.9 / 54.8 ms
     return cudaGetLastError();

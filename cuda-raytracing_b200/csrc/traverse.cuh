@@ -304,109 +304,6 @@ __device__ __forceinline__ void trace_wide(const AccelView& A, Vec3 o, Vec3 d, V
     trace_wide_checked<kTieById>(A, o, d, nd, h);
 }
 
-__device__ __forceinline__ void sphere_tests(const RtSphere* spheres, int count, Vec3 o, Vec3 nd, HitRecord& h);
-
-// ------------------------------------------------------------------------------------------------
-// Batched traversal: ONE traversal loop over up to K rays of a lane, one after the other.
-// A warp's loop runs until its slowest lane is done, and single-ray lengths are spread like an exponential: with one ray per lane
-// a round lasts E[max of 32] ~ 4 x the mean ray, i.e. three quarters of the lane-iterations idle. A lane that owns K independent
-// rays (K pixels) and switches to its next ray INSIDE the loop makes the round last the max of 32 sums of K - the sum's relative
-// spread shrinks like 1 / sqrt(K), so fewer lanes wait for the slowest one. The switch (store 5 result words, load 8, three
-// MUFU.RCP) is the only code that runs per ray at low lane counts; everything else of a ray's set-up stays outside the loop.
-// Per ray: the same steps in the same order as trace_wide_impl<kTieById, true> - results are bit-identical.
-// ------------------------------------------------------------------------------------------------
-struct RayRecord
-{
-    Vec3 o, d, nd;          // origin, direction as given, normalised direction
-    float t0;               // in: distance the search starts with (sphere hit or 1e30); < 0 = this slot holds no ray
-    float t; uint32_t id;   // in: the sphere result (t = t0); out: the closest hit
-    uint32_t slot;          // in: sphere index; out: BVH slot of a triangle hit
-    float bu, bv;
-};
-
-template <bool kTieById, int K>
-__device__ __forceinline__ void trace_wide_batch(const AccelView& A, RayRecord* rec, uint32_t* work = nullptr)
-{
-    const float kWiden = 1.0e-6f;
-    uint32_t stack[RT_STACK_SIZE];
-    uint32_t* sp = stack;
-    uint32_t node = RT_SENTINEL;
-    int j = -1;
-    Vec3 o = mk3(0, 0, 0), nd = mk3(0, 0, 0);
-    SlabRay R = make_slab_ray(o, mk3(1, 1, 1));
-    HitRecord h; h.t = 0; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
-    for (;;)
-    {
-        if (node == RT_SENTINEL)
-        {   // this lane's current ray is done (or none was started yet): hand in the result, take the next ray
-            if (j >= 0) { rec[j].t = h.t; rec[j].id = h.id; rec[j].slot = h.slot; rec[j].bu = h.bu; rec[j].bv = h.bv; }
-            do { j++; } while (j < K && rec[j].t0 < 0.0f);
-            if (j >= K) break;
-            o = rec[j].o; nd = rec[j].nd;
-            R = make_slab_ray(o, nd);
-            h.t = rec[j].t0; h.id = rec[j].id; h.slot = rec[j].slot; h.key = (h.id & RT_SPHERE_ID_BIT) ? 0u : RT_MISS_ID; h.bu = 0; h.bv = 0;
-            sp = stack; *sp++ = RT_SENTINEL;
-            node = A.root_ref;
-            continue;
-        }
-        const bool is_leaf = (node & RT_LEAF_BIT) != 0u;
-        const uint32_t slot = node & RT_REF_BYTE_MASK;
-        const char* recp = A.arena + slot;
-        const float4 q0 = ldg4(recp), q1 = ldg4(recp + 16), q2 = ldg4(recp + 32);
-        const uint2 q3 = __ldg(reinterpret_cast<const uint2*>(recp + 48));
-        if (!is_leaf)
-        {
-            if (work) work[0]++;
-            float mn0, mx0, mn1, mx1;
-            center_slabs(q0, q1, q2, R.no_xy, R.no_zz, R.i_xy, R.i_zz, R.ai_xy, R.ai_zz, mn0, mx0, mn1, mx1);
-            const float lo0 = fmaf(-kWiden, fabsf(mn0), mn0), hi0 = fmaf(kWiden, fabsf(mx0), mx0);
-            const float lo1 = fmaf(-kWiden, fabsf(mn1), mn1), hi1 = fmaf(kWiden, fabsf(mx1), mx1);
-            const bool hit0 = hi0 >= lo0 && lo0 <= h.t && hi0 > 0.0f;
-            const bool hit1 = hi1 >= lo1 && lo1 <= h.t && hi1 > 0.0f;
-            if (hit0 && hit1)
-            {
-                const bool swap = mn1 < mn0;
-                *sp++ = swap ? q3.x : q3.y;
-                node = swap ? q3.y : q3.x;
-            }
-            else if (hit0) node = q3.x;
-            else if (hit1) node = q3.y;
-            else node = *--sp;
-        }
-        else
-        {
-            if (work) work[1]++;
-            leaf_test_one<false, kTieById>(A, q0, q1, q2, slot, o, nd, nd, 0.0f, h);
-            if (ref_has_more(node)) node = ref_next_tri(node);
-            else node = *--sp;
-        }
-    }
-}
-
-// After trace_wide_batch: the deferred check of ray j's winner against its reference leaf box (main_raytracing.cu:46) and the rare
-// redo with the per-candidate check. Returns the ray's final hit record.
-template <bool kTieById>
-__device__ __forceinline__ HitRecord finish_batched_ray(const AccelView& A, const RtSphere* spheres, int sphere_count, const RayRecord& r)
-{
-    HitRecord h; h.t = r.t; h.id = r.id; h.slot = r.slot; h.key = 0; h.bu = r.bu; h.bv = r.bv;
-    if (h.id != RT_MISS_ID && !(h.id & RT_SPHERE_ID_BIT))
-    {
-        h.slot = offset_slot(A, h.slot);  // the loop leaves the winner's arena byte offset
-        const uint32_t leaf = __ldg(&A.tris[h.slot].ref_leaf) & RT_REF_LEAF_MASK;
-        bool ok = exact_box(r.o, r.d, A.ref_nodes + leaf, r.t0);
-#ifdef RT_TW_FORCE_REDO
-        if ((h.slot & RT_TW_FORCE_REDO) == 0u) ok = false;
-#endif
-        if (!ok)
-        {
-            h.t = 1e30f; h.id = RT_MISS_ID; h.slot = 0; h.key = RT_MISS_ID; h.bu = 0; h.bv = 0;
-            sphere_tests(spheres, sphere_count, r.o, r.nd, h);
-            trace_wide_checked<kTieById>(A, r.o, r.d, r.nd, h);
-        }
-    }
-    return h;
-}
-
 // Reference-order traversal over the reference-layout nodes: right child first, exact box test at
 // every node against the CURRENT best (main_raytracing.cu:43-78). By-construction parity kernel.
 template <bool kTieById>

@@ -134,8 +134,7 @@ typedef struct RtProcessParams
                                    finished rays are parked, shaded and refilled together by warp ballot; bit-identical image),
                                    2 = measurement: reference traversal order + d_work_counters (nodes popped, triangle tests),
                                    3 = measurement: the megakernel with d_work_counters (wide-node steps, triangle tests executed),
-                                   4..9 = batched megakernel: K = 2, 3, 4 pixels per lane, one traversal loop over the lane's K rays
-                                          (4-6 at 48 registers, 7-9 at 64); bit-identical, measured slower,
+                                   (4..9, 11, 12: measured-and-rejected kernels that live as patches under profiles/experiments/),
                                    10 = queue-based wavefront: one stage per ray depth, path state in HBM, ballot / prefix-sum
                                         compaction into camera + direction-octant queues between stages; needs the workspace of
                                         rt_process_workspace_bytes(width, height, 10); bit-identical, measured 2x slower */

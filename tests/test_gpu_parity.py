@@ -480,12 +480,11 @@ def test_regroup_variant_bit_identical_to_megakernel(rt, torch_cuda, size):
     assert t.equal(sa, sb)
 
 
-@pytest.mark.parametrize("variant", [4, 6, 8, 10])
-def test_batched_and_wavefront_variants_bit_identical_to_megakernel(rt, torch_cuda, variant):
-    """variants 4-9 (batched megakernel: K pixels per lane, one traversal loop over a lane's K rays) and variant 10 (queue-based
-    wavefront: path state in HBM, ballot / prefix-sum compaction into camera + octant queues between stages, north-star item 3) run
-    the same per-pixel sequence of draws and fp32 operations as variant 0: surfaces, RNG states and ray counts are identical.
-    Frame sizes that do not fill the tiles; running-mean and sum blend."""
+@pytest.mark.parametrize("variant", [10])
+def test_wavefront_variant_bit_identical_to_megakernel(rt, torch_cuda, variant):
+    """variant 10 (queue-based wavefront: path state in HBM, ballot / prefix-sum compaction into camera + octant queues between
+    stages, north-star item 3) runs the same per-pixel sequence of draws and fp32 operations as variant 0: surfaces, RNG states
+    and ray counts are identical. Frame sizes that do not fill the tiles; running-mean and sum blend."""
     t = torch_cuda
     for (W, H) in ((200, 120), (37, 23)):
         a = gpu_util.DeviceScene(rt, t, W, H, "poseB", seed=21, env=True)

@@ -37,7 +37,9 @@
 // results). Half extents are rounded up and inflated by 2^-21 (+ the centre's own rounding) at build time, so the stored box is a
 // superset; exactness is the reference-leaf check's business (traverse.cuh).
 #define RT_REF_LEAF_MASK 0x7FFFFFFFu
-#define RT_STACK_SIZE 64
+#ifndef RT_STACK_SIZE
+#define RT_STACK_SIZE 64   /* traversal stack entries per thread (local memory); the builder refuses deeper trees */
+#endif
 
 struct RtFloat4 { float x, y, z, w; };
 

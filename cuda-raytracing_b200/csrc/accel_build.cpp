@@ -164,6 +164,206 @@ namespace
             wn.child[0] = c0; wn.child[1] = c1;
             return w;
         }
+
+        // ---- own topology over the reference's leaves -------------------------------------------------------------------
+        // The hit rule (smallest t, ties to the lowest reference visiting order) and the deferred exact reference-leaf box
+        // check (traverse.cuh) make the result a function of WHICH triangles a ray is tested against, not of the tree above
+        // them: any binary tree whose boxes hold the exact reference leaf boxes below them returns the reference's hits.
+        // BVH.cpp:61-107 splits at the spatial midpoint of the longest axis; this builds a surface-area-heuristic tree over the
+        // SAME leaves (slots, leaf contents and TriRecords untouched: the reference-order kernels keep reading them as they are).
+        struct Item { Box box; float cen[3]; uint32_t ref; float weight; };
+        std::vector<Item> items;
+        uint32_t fat_depth = 0;
+
+        // reference leaves in visiting order; fat ones get their private sub-tree (appended to out.wide) first
+        void CollectLeaves()
+        {
+            std::vector<std::pair<uint32_t, uint32_t>> stack; stack.push_back({ 0u, 0u });
+            uint64_t visited = 0;
+            while (!stack.empty() && !error)
+            {
+                const auto [n, depth] = stack.back(); stack.pop_back();
+                if (n >= node_count || ++visited > node_count) { error = RT_E_INVALID; return; }
+                const RtBVHNode& node = nodes[n];
+                out.ref_depth = std::max(out.ref_depth, depth);
+                if (node.prim_count == 0)
+                {
+                    if (depth > 4096) { error = RT_E_DEPTH; return; }
+                    stack.push_back({ node.first_index + 1, depth + 1 }); stack.push_back({ node.first_index, depth + 1 });
+                    continue;
+                }
+                out.ref_leaf_count++;
+                if ((uint64_t)node.first_index + node.prim_count > out.tris.size()) { error = RT_E_INVALID; return; }
+                for (uint32_t s = node.first_index; s < node.first_index + node.prim_count; s++) out.tris[s].ref_leaf = n;
+                Item it;
+                it.box = FromNode(node);
+                for (int k = 0; k < 3; k++) it.cen[k] = 0.5f * it.box.lo[k] + 0.5f * it.box.hi[k];
+                if (node.prim_count <= threshold) { it.ref = LeafRef(node.first_index, node.prim_count); it.weight = (float)node.prim_count; }
+                else
+                {
+                    out.fat_leaf_count++;
+                    const uint32_t before = out.wide_depth;
+                    out.wide_depth = 0;
+                    Box unused;
+                    it.ref = BuildSub(node.first_index, node.prim_count, 0, unused);
+                    fat_depth = std::max(fat_depth, out.wide_depth);
+                    out.wide_depth = before;
+                    it.weight = 2.0f * std::log2((float)node.prim_count) + 4.0f;  // expected steps inside the sub-tree
+                }
+                items.push_back(it);
+            }
+        }
+
+        static uint32_t CeilLog2(uint32_t n) { uint32_t d = 0; while ((1ull << d) < n) d++; return d; }
+
+        // Partitions items[lo, hi) (hi - lo >= 2) and returns the split position m (lo < m < hi).
+        uint32_t Split(uint32_t lo, uint32_t hi, bool balanced)
+        {
+            const uint32_t n = hi - lo;
+            Item* it = items.data() + lo;
+            Box cb = EmptyBox();
+            for (uint32_t i = 0; i < n; i++) Grow(cb, it[i].cen);
+            int widest = 0;
+            for (int k = 1; k < 3; k++) if (cb.hi[k] - cb.lo[k] > cb.hi[widest] - cb.lo[widest]) widest = k;
+            auto median = [&]() -> uint32_t
+            {
+                if (cb.hi[widest] > cb.lo[widest])
+                    std::nth_element(it, it + n / 2, it + n, [&](const Item& a, const Item& b) { return a.cen[widest] < b.cen[widest]; });
+                return lo + n / 2;
+            };
+            if (balanced || n == 2) return median();
+            if (n <= 1024)
+            {   // full sweep on the three axes
+                float best_cost = 3.4e38f; int best_axis = -1, sorted_axis = -1; uint32_t best_split = 0;
+                std::vector<float> right_area(n), right_weight(n);
+                for (int axis = 0; axis < 3; axis++)
+                {
+                    if (!(cb.hi[axis] > cb.lo[axis])) continue;
+                    std::stable_sort(it, it + n, [&](const Item& a, const Item& b) { return a.cen[axis] < b.cen[axis]; });
+                    sorted_axis = axis;
+                    Box acc = EmptyBox(); float w = 0;
+                    for (uint32_t i = n; i-- > 0;) { Grow(acc, it[i].box); w += it[i].weight; right_area[i] = HalfArea(acc); right_weight[i] = w; }
+                    acc = EmptyBox(); w = 0;
+                    for (uint32_t i = 0; i + 1 < n; i++)
+                    {
+                        Grow(acc, it[i].box); w += it[i].weight;
+                        const float cost = HalfArea(acc) * w + right_area[i + 1] * right_weight[i + 1];
+                        if (cost < best_cost) { best_cost = cost; best_axis = axis; best_split = i + 1; }
+                    }
+                }
+                if (best_axis < 0) return median();
+                if (best_axis != sorted_axis) std::stable_sort(it, it + n, [&](const Item& a, const Item& b) { return a.cen[best_axis] < b.cen[best_axis]; });
+                return lo + best_split;
+            }
+            // binned
+            constexpr int kBins = 32;
+            float best_cost = 3.4e38f; int best_axis = -1, best_plane = 0;
+            for (int axis = 0; axis < 3; axis++)
+            {
+                const float extent = cb.hi[axis] - cb.lo[axis];
+                if (!(extent > 0)) continue;
+                const float scale = (float)kBins / extent;
+                Box bin_box[kBins]; float bin_weight[kBins]; uint32_t bin_count[kBins];
+                for (int b = 0; b < kBins; b++) { bin_box[b] = EmptyBox(); bin_weight[b] = 0; bin_count[b] = 0; }
+                for (uint32_t i = 0; i < n; i++)
+                {
+                    const int b = std::min(kBins - 1, std::max(0, (int)((it[i].cen[axis] - cb.lo[axis]) * scale)));
+                    Grow(bin_box[b], it[i].box); bin_weight[b] += it[i].weight; bin_count[b]++;
+                }
+                float right_area[kBins], right_weight[kBins]; uint32_t right_count[kBins];
+                Box acc = EmptyBox(); float w = 0; uint32_t c = 0;
+                for (int b = kBins; b-- > 0;) { if (bin_count[b]) Grow(acc, bin_box[b]); w += bin_weight[b]; c += bin_count[b]; right_area[b] = HalfArea(acc); right_weight[b] = w; right_count[b] = c; }
+                acc = EmptyBox(); w = 0; c = 0;
+                for (int b = 0; b + 1 < kBins; b++)
+                {
+                    if (bin_count[b]) Grow(acc, bin_box[b]);
+                    w += bin_weight[b]; c += bin_count[b];
+                    if (c == 0 || right_count[b + 1] == 0) continue;
+                    const float cost = HalfArea(acc) * w + right_area[b + 1] * right_weight[b + 1];
+                    if (cost < best_cost) { best_cost = cost; best_axis = axis; best_plane = b; }
+                }
+            }
+            if (best_axis < 0) return median();
+            const float scale = (float)kBins / (cb.hi[best_axis] - cb.lo[best_axis]);
+            const float origin = cb.lo[best_axis];
+            Item* mid = std::partition(it, it + n, [&](const Item& a)
+            { return std::min(kBins - 1, std::max(0, (int)((a.cen[best_axis] - origin) * scale))) <= best_plane; });
+            const uint32_t m = lo + (uint32_t)(mid - it);
+            return (m == lo || m == hi) ? median() : m;
+        }
+
+        // Sub-tree over items[lo, hi) (>= 2 items) rooted at out.wide[node]; the sub-tree occupies out.wide[node, node + (hi - lo) - 1)
+        // in pre-order, so the index of every node follows from the split positions alone (tasks need no shared counter).
+        void BuildOwn(uint32_t lo, uint32_t hi, uint32_t node, uint32_t depth, uint32_t depth_limit)
+        {
+            const uint32_t n = hi - lo;
+            const bool balanced = depth + 1 + CeilLog2(n) >= depth_limit;  // SAH may chain: from here on halve by count
+            const uint32_t m = Split(lo, hi, balanced);
+            Box b0 = EmptyBox(), b1 = EmptyBox();
+            for (uint32_t i = lo; i < m; i++) Grow(b0, items[i].box);
+            for (uint32_t i = m; i < hi; i++) Grow(b1, items[i].box);
+            WideNode& w = out.wide[node];
+            SetChildBox(w, 0, b0); SetChildBox(w, 1, b1);   // unions of exact reference leaf boxes; SetChildBox rounds outwards
+            const uint32_t left = node + 1, right = node + (m - lo);
+            w.child[0] = (m - lo == 1) ? items[lo].ref : left;
+            w.child[1] = (hi - m == 1) ? items[m].ref : right;
+            w.pad[0] = w.pad[1] = 0;
+            if (m - lo >= 2)
+            {
+#pragma omp task default(shared) firstprivate(lo, m, left, depth, depth_limit) if (m - lo > 20000)
+                BuildOwn(lo, m, left, depth + 1, depth_limit);
+            }
+            if (hi - m >= 2)
+            {
+#pragma omp task default(shared) firstprivate(m, hi, right, depth, depth_limit) if (hi - m > 20000)
+                BuildOwn(m, hi, right, depth + 1, depth_limit);
+            }
+        }
+
+        // Root reference of the own-topology tree (RT_SENTINEL + error on failure).
+        uint32_t BuildOwnTopology()
+        {
+            // reserve the own tree's nodes at the front (root = wide[0]); fat-leaf sub-trees are appended behind them
+            uint32_t leaves = 0;
+            {
+                std::vector<uint32_t> stack; stack.push_back(0);
+                uint64_t visited = 0;
+                while (!stack.empty())
+                {
+                    const uint32_t n = stack.back(); stack.pop_back();
+                    if (n >= node_count || ++visited > node_count) { error = RT_E_INVALID; return RT_SENTINEL; }
+                    if (nodes[n].prim_count) leaves++;
+                    else { stack.push_back(nodes[n].first_index); stack.push_back(nodes[n].first_index + 1); }
+                }
+            }
+            out.wide.assign(leaves > 1 ? leaves - 1 : 0, WideNode{});
+            items.reserve(leaves);
+            CollectLeaves();
+            if (error) return RT_SENTINEL;
+            if (items.size() != leaves) { error = RT_E_INVALID; return RT_SENTINEL; }
+            if (leaves == 1) return items[0].ref;
+            if (CeilLog2(leaves) + fat_depth + 4 > RT_STACK_SIZE) { error = RT_E_DEPTH; return RT_SENTINEL; }
+            const uint32_t depth_limit = RT_STACK_SIZE - 3 - fat_depth;
+#pragma omp parallel
+#pragma omp single
+            BuildOwn(0, leaves, 0, 0, depth_limit);
+            return 0;
+        }
+
+        // depth of the finished tree (internal index references), by walking it
+        uint32_t MeasureDepth(uint32_t root) const
+        {
+            uint32_t deepest = 0;
+            std::vector<std::pair<uint32_t, uint32_t>> stack; stack.push_back({ root, 0u });
+            while (!stack.empty())
+            {
+                const auto [ref, depth] = stack.back(); stack.pop_back();
+                if (ref == RT_SENTINEL || (ref & RT_LEAF_BIT)) continue;
+                deepest = std::max(deepest, depth + 1);
+                stack.push_back({ out.wide[ref].child[0], depth + 1 }); stack.push_back({ out.wide[ref].child[1], depth + 1 });
+            }
+            return deepest;
+        }
     };
 }
 
@@ -203,8 +403,17 @@ int BuildAccelHost(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* 
     if (invalid) return RT_E_INVALID;
     lap("gather records");
     Builder builder{ nodes, node_count, fat_leaf_threshold, out, {}, {}, 0 };
-    out.wide.reserve(node_count / 2 + 16);
-    out.root_ref = builder.Emit(0, 0);
+    const char* topology = std::getenv("B200RT_TOPOLOGY");
+    if (topology && !std::strcmp(topology, "ref"))
+    {   // the reference's own midpoint-split topology (A/B switch)
+        out.wide.reserve(node_count / 2 + 16);
+        out.root_ref = builder.Emit(0, 0);
+    }
+    else
+    {
+        out.root_ref = builder.BuildOwnTopology();
+        if (!builder.error) out.wide_depth = builder.MeasureDepth(out.root_ref);
+    }
     lap("wide nodes");
     if (builder.error) return builder.error;
     if (out.wide_depth + 2 > RT_STACK_SIZE || out.ref_depth + 2 > RT_STACK_SIZE) return RT_E_DEPTH;
@@ -222,6 +431,30 @@ int BuildAccelHost(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* 
     for (WideNode& w : out.wide) { w.child[0] = to_offset(w.child[0]); w.child[1] = to_offset(w.child[1]); }
     out.root_ref = to_offset(out.root_ref);
     lap("byte-offset refs");
+    if (timing && !(out.root_ref & RT_LEAF_BIT))
+    {   // expected steps of a random ray that hits the root box (surface-area measure): one node step per entered inner child, one
+        // triangle step per triangle of an entered leaf
+        auto area = [&](const WideNode& w, int c) { float ctr[3], h[3]; ChildCentreHalf(w, c, ctr, h); return h[0] < 0 ? 0.0 : 4.0 * ((double)h[0] * h[1] + (double)h[1] * h[2] + (double)h[2] * h[0]); };
+        Box rb = EmptyBox();
+        for (int c = 0; c < 2; c++)
+        {
+            float ctr[3], h[3]; ChildCentreHalf(out.wide[0], c, ctr, h);
+            if (h[0] < 0) continue;
+            float lo[3], hi[3];
+            for (int k = 0; k < 3; k++) { lo[k] = ctr[k] - h[k]; hi[k] = ctr[k] + h[k]; }
+            Grow(rb, lo); Grow(rb, hi);
+        }
+        const double root_area = HalfArea(rb);
+        double node_steps = 1.0, tri_steps = 0.0;
+        for (const WideNode& w : out.wide)
+            for (int c = 0; c < 2; c++)
+            {
+                if (w.child[c] == RT_SENTINEL) continue;
+                const double a = area(w, c) / root_area;
+                if (w.child[c] & RT_LEAF_BIT) tri_steps += a * ((w.child[c] & RT_REF_COUNT_MASK) + 1u); else node_steps += a;
+            }
+        std::fprintf(stderr, "[accel] surface-area cost: %.2f node steps + %.2f triangle steps = %.2f, depth %u\n", node_steps, tri_steps, node_steps + tri_steps, out.wide_depth);
+    }
     return 0;
 }
 

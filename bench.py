@@ -205,7 +205,8 @@ def csrc_hash():
     import hashlib
     h = hashlib.sha1()
     d = os.path.join(ROOT, "cuda-raytracing_b200", "csrc")
-    for name in ("accel.h", "kernels.h", "pathtrace.cu", "pathtrace_common.cuh", "rng.cuh", "shade.cuh", "traverse.cuh"):  # what the megakernel is compiled from
+    # what the megakernel is compiled from, and the builder of the tree it walks (the tree decides the instructions per ray)
+    for name in ("accel.h", "accel_build.cpp", "kernels.h", "pathtrace.cu", "pathtrace_common.cuh", "rng.cuh", "shade.cuh", "traverse.cuh"):
         h.update(name.encode()); h.update(open(os.path.join(d, name), "rb").read())
     return h.hexdigest()[:16]
 

@@ -34,6 +34,7 @@ def main():
     ap.add_argument("--grid", action="store_true")
     ap.add_argument("--variant", type=int, default=0)
     ap.add_argument("--no-hash", action="store_true")
+    ap.add_argument("--counters", action="store_true", help="wide-node steps and triangle tests per ray of the shipped kernel (variant 3, 2 spp)")
     a = ap.parse_args()
     rt = load_package()
     out = {"lib": os.path.basename(os.environ.get("B200RT_LIB", "libb200rt.so")), "variant": a.variant}
@@ -56,6 +57,15 @@ def main():
     d.counter.zero_()
     ms = timed(f, a.steps, flush)
     out.update({"ms_median": sorted(ms)[len(ms) // 2], "ms_min": min(ms), "ms_max": max(ms), "mrays_s": d.rays() / sum(ms) / 1e3})
+    if a.counters:
+        from cuda_raytracing_b200.api import process_ex
+        work = torch.zeros(2, dtype=torch.int64, device="cuda")
+        d.counter.zero_()
+        process_ex(d.surface, d.last, W, H, d.pitch, 0, d.gpu, d.accel, spp=2, bounces=4, blend_mode=0, variant=3, ray_counter=d.counter,
+                   stream=torch.cuda.current_stream().cuda_stream, work_counters=work)
+        torch.cuda.synchronize()
+        rays = int(d.counter.item())
+        out.update({"node_steps_per_ray": work[0].item() / rays, "tri_tests_per_ray": work[1].item() / rays})
     if a.grid:
         import scaled_meshes
         del d

@@ -98,10 +98,12 @@ REDO_LIB = os.path.join(LIB_DIR, "libb200rt_redo.so")
 
 def build_redo_variant(force=False):
     """Test build (tests/test_gpu_redo_build.py): RT_TW_FORCE_REDO=7 sends every ray whose winning slot is a multiple of 8 through
-    the redo path of trace_wide (per-candidate exact leaf-box check), which a grazing ray takes about never."""
+    the redo path of trace_wide (per-candidate exact leaf-box check), which a grazing ray takes about never; RT_STACK_SIZE=32 (64 in
+    the product) makes the builder's depth limiter - SAH splits replaced by halving near the end of the traversal stack - work on
+    the bunny scene, whose SAH tree is 21 levels deep with an 8-level fat-leaf sub-tree below."""
     if not force and os.path.exists(REDO_LIB) and os.path.getmtime(REDO_LIB) >= _newest_source_mtime():
         return REDO_LIB
-    return build(defines=["RT_TW_FORCE_REDO=7"], out="libb200rt_redo.so")
+    return build(defines=["RT_TW_FORCE_REDO=7", "RT_STACK_SIZE=32"], out="libb200rt_redo.so")
 
 
 if __name__ == "__main__":

@@ -13,8 +13,9 @@ import util
 pytestmark = pytest.mark.gpu
 
 
-def run(cmd, lib):
+def run(cmd, lib, extra_env=None):
     env = dict(os.environ)
+    env.update(extra_env or {})
     if lib:
         env["B200RT_LIB"] = lib
     else:
@@ -34,3 +35,14 @@ def test_forced_redo_build_is_bit_identical(rt, torch_cuda):
     t = run(["-m", "pytest", "tests/test_gpu_parity.py", "-m", "gpu", "-q", "-x", "-k",
              "primary_hits_vs_reference_golden or incoherent_rays_vs_reference_golden or fresh_random_rays"], redo)
     assert t.returncode == 0, t.stdout[-3000:]
+
+
+def test_own_tree_and_reference_topology_give_the_same_frames(rt, torch_cuda):
+    """The wide tree's topology is the product's own (SAH + insertion-based optimisation over the reference's leaves, accel_build.cpp);
+    B200RT_TOPOLOGY=ref re-lays out BVH.cpp's midpoint tree as it is, B200RT_REINSERT=0 stops after the SAH build. The frames and RNG
+    states may not depend on it."""
+    a = run(["benchmarks/frame_hash.py"], None)
+    b = run(["benchmarks/frame_hash.py"], None, {"B200RT_TOPOLOGY": "ref"})
+    c = run(["benchmarks/frame_hash.py"], None, {"B200RT_REINSERT": "0"})
+    assert a.returncode == 0 and b.returncode == 0 and c.returncode == 0, (a.stderr[-2000:], b.stderr[-2000:], c.stderr[-2000:])
+    assert a.stdout.strip().splitlines()[-1] == b.stdout.strip().splitlines()[-1] == c.stdout.strip().splitlines()[-1]

@@ -187,6 +187,38 @@ def test_accel_relayout_structure_on_the_host(rt, bunny):
         check(scene.arrays(), 0)
 
 
+def test_own_topology_over_the_reference_leaves(rt, bunny, monkeypatch):
+    """accel_build.cpp builds its own SAH tree (+ one insertion-based optimisation pass) over the reference's leaves; B200RT_TOPOLOGY=ref
+    keeps BVH.cpp's midpoint tree. Both are binary trees over the same leaves and pass the same host check (containment of the exact
+    reference leaf boxes, replay of the kernel's node test); a build with a 32-entry traversal stack (the test build) has the builder halve by count where SAH
+    splits would leave the stack, and still passes."""
+    def check(a):
+        info = (C.c_uint64 * 4)()
+        r = rt.lib().rt_accel_check_host(rt.ptr(a["nodes"]), len(a["nodes"]), rt.ptr(a["face_indices"]), rt.ptr(a["faces"]), len(a["faces"]),
+                                         rt.ptr(a["vertices"]), len(a["vertices"]), 0, info)
+        assert r == 0, rt.lib().rt_last_error()
+        return [int(v) for v in info]
+    a = bunny["arrays"]
+    own = check(a)
+    monkeypatch.setenv("B200RT_REINSERT", "0")
+    sah_only = check(a)
+    monkeypatch.setenv("B200RT_TOPOLOGY", "ref")
+    ref_tree = check(a)
+    monkeypatch.delenv("B200RT_TOPOLOGY"); monkeypatch.delenv("B200RT_REINSERT")
+    assert own[:2] == sah_only[:2] == ref_tree[:2] and own[3] == ref_tree[3]   # same leaves, same number of inner nodes, same arena
+    assert own[2] < 40 and ref_tree[2] < 40
+    # the depth limiter: the test build has a 32-entry traversal stack (build.py build_redo_variant)
+    from _loader import load_build
+    small = C.CDLL(load_build().REDO_LIB)
+    small.rt_accel_check_host.restype = C.c_int
+    small.rt_accel_check_host.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64)]
+    info = (C.c_uint64 * 4)()
+    r = small.rt_accel_check_host(rt.ptr(a["nodes"]), len(a["nodes"]), rt.ptr(a["face_indices"]), rt.ptr(a["faces"]), len(a["faces"]),
+                                  rt.ptr(a["vertices"]), len(a["vertices"]), 0, info)
+    assert r == 0
+    assert list(info)[:2] == own[:2] and info[2] + 2 <= 32
+
+
 def test_golden_hashes(rt, bunny):
     """Runs everywhere (no /root/reference needed): arrays hash to what the GLM + BVH.cpp build produced."""
     h = json.load(open(os.path.join(util.GOLDEN, "scene_hashes.json")))

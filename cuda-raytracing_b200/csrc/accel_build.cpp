@@ -593,14 +593,18 @@ int BuildAccelHost(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* 
             Grow(rb, lo); Grow(rb, hi);
         }
         const double root_area = HalfArea(rb);
-        double node_steps = 1.0, tri_steps = 0.0;
-        for (const WideNode& w : out.wide)
+        double node_steps = 1.0, tri_steps = 0.0, sub_node_steps = 0.0, sub_tri_steps = 0.0;
+        const size_t own_nodes = out.ref_leaf_count > 1 ? out.ref_leaf_count - 1 : 0;   // the fat leaves' private sub-trees follow them
+        for (size_t i = 0; i < out.wide.size(); i++)
             for (int c = 0; c < 2; c++)
             {
+                const WideNode& w = out.wide[i];
                 if (w.child[c] == RT_SENTINEL) continue;
                 const double a = area(w, c) / root_area;
-                if (w.child[c] & RT_LEAF_BIT) tri_steps += a * ((w.child[c] & RT_REF_COUNT_MASK) + 1u); else node_steps += a;
+                if (w.child[c] & RT_LEAF_BIT) { tri_steps += a * ((w.child[c] & RT_REF_COUNT_MASK) + 1u); if (i >= own_nodes) sub_tri_steps += a * ((w.child[c] & RT_REF_COUNT_MASK) + 1u); }
+                else { node_steps += a; if (i >= own_nodes) sub_node_steps += a; }
             }
+        if (builder.items.size()) std::fprintf(stderr, "[accel] of which inside fat-leaf sub-trees: %.2f node steps + %.2f triangle steps (%u fat leaves)\n", sub_node_steps, sub_tri_steps, out.fat_leaf_count);
         std::fprintf(stderr, "[accel] surface-area cost: %.2f node steps + %.2f triangle steps = %.2f, depth %u\n", node_steps, tri_steps, node_steps + tri_steps, out.wide_depth);
     }
     return 0;

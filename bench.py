@@ -151,8 +151,10 @@ class ClockSampler:
         self.proc = None
         try:
             self.f = open(self.path, "w")
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(index)],
-                                         stdout=self.f, stderr=subprocess.DEVNULL)
+            cmd = ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"]
+            if index is not None:   # None = every GPU of the node (multi-rank runs: the step time is the slowest rank's)
+                cmd += ["-i", str(index)]
+            self.proc = subprocess.Popen(cmd, stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
 
@@ -165,13 +167,14 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
         self.f.close()
-        sm, mx, reasons = [], [], set()
+        sm, mx, reasons, per_gpu = [], [], set(), {}
         for line in open(self.path):
             c = [x.strip() for x in line.split(",")]
             if len(c) < 9:
                 continue
             try:
                 sm.append(float(c[1])); mx.append(float(c[2]))
+                per_gpu.setdefault(c[0], ([], []))[0].append(float(c[1])); per_gpu[c[0]][1].append(float(c[3]))
             except ValueError:
                 continue
             for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[5:9]):
@@ -183,7 +186,10 @@ class ClockSampler:
             pass
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
-        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+        out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+        if len(per_gpu) > 1:
+            out["per_gpu"] = {k: {"sm_mhz": float(np.median(v[0])), "sm_mhz_min": float(min(v[0])), "power_w": float(np.median(v[1]))} for k, v in sorted(per_gpu.items())}
+        return out
 
 
 # ------------------------------------------------------------------------------------------------
@@ -316,7 +322,7 @@ def run_b200_arm(a):
     torch.cuda.synchronize()
     d.counter.zero_()
     uuid = str(torch.cuda.get_device_properties(local).uuid)
-    sampler = ClockSampler(uuid if uuid.startswith("GPU-") else "GPU-" + uuid) if rank == 0 else None
+    sampler = ClockSampler((uuid if uuid.startswith("GPU-") else "GPU-" + uuid) if world == 1 else None) if rank == 0 else None
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
     wall0 = time.perf_counter()
     for k in range(a.steps):
@@ -342,9 +348,12 @@ def run_b200_arm(a):
     if world > 1:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        per_rank = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(per_rank, t)
+        per_rank_ms = [round(x[0].item() / a.steps, 3) for x in per_rank]
         step_ms, kern_ms, rays_all = tmax[0].item(), tmax[1].item(), tsum[2].item()
     else:
-        rays_all = float(rays)
+        rays_all = float(rays); per_rank_ms = None
     value = rays_all / (step_ms * 1e-3) / 1e6
 
     # ---- e2e: the headless facade call with HOST buffers ----
@@ -413,7 +422,8 @@ def run_b200_arm(a):
                                "the first launch after a resize or camera jump runs in grid order (see config.first_launch_ms)",
                    "first_launch_ms": first_launch_ms,
                    "parallelism": "1 GPU" if world == 1 else f"spp split: {world} ranks x {a.spp} spp, disjoint XORWOW subsequences, 1 NCCL reduce(sum fp32) of the frame per step",
-                   "rays_per_step": rays_all / a.steps, "ms_per_frame_64spp": step_ms / a.steps, "wall_s": wall},
+                   "rays_per_step": rays_all / a.steps, "ms_per_frame_64spp": step_ms / a.steps, "wall_s": wall,
+                   **({"ms_per_step_per_rank": per_rank_ms} if per_rank_ms else {})},
         "clocks": clocks, "gpu_launches": launches * (2 if a.variant == 0 else 1), "roofline": roofline,
     }
     if strong:

@@ -55,7 +55,9 @@ namespace
         float c[3], h[3];
         for (int k = 0; k < 3; k++)
         {   // [c - h, c + h] in exact arithmetic holds [lo, hi]; h carries the 2^-21 the kernel's rounding of h * |1/d| needs
-            const double lo = b.lo[k], hi = b.hi[k];
+            // (infinite bounds - a vertex at infinity - become +-1.7e38: everything the kernels can reach lies inside, and centre and
+            // half extent stay finite)
+            const double lo = std::max((double)b.lo[k], -1.7e38), hi = std::min((double)b.hi[k], 1.7e38);
             c[k] = (float)(0.5 * (lo + hi));
             if (!(lo <= hi)) { c[k] = 0.0f; h[k] = -1e30f; continue; }  // empty box: exit far before entry, never hit
             const double need = std::max(hi - (double)c[k], (double)c[k] - lo) * (1.0 + 4.8e-7) + 1e-37;
@@ -116,7 +118,9 @@ namespace
                     if (cost < best_cost) { best_cost = cost; best_axis = axis; best_split = i + 1; }
                 }
             }
-            // apply the best permutation
+            // apply the best permutation (no finite cost on any axis - NaN / infinite vertices: halve the range as it stands)
+            if (best_axis < 0 || best_split == 0 || best_split >= count) best_split = count / 2;
+            else
             {
                 std::vector<float> cen(count);
                 for (uint32_t i = 0; i < count; i++) { const Box b = SlotBox(first + i); cen[i] = b.lo[best_axis] + b.hi[best_axis]; }
@@ -202,7 +206,7 @@ namespace
                 for (uint32_t s = node.first_index; s < node.first_index + node.prim_count; s++) out.tris[s].ref_leaf = n;
                 Item it;
                 it.box = FromNode(node);
-                for (int k = 0; k < 3; k++) it.cen[k] = 0.5f * it.box.lo[k] + 0.5f * it.box.hi[k];
+                for (int k = 0; k < 3; k++) { it.cen[k] = 0.5f * it.box.lo[k] + 0.5f * it.box.hi[k]; if (!std::isfinite(it.cen[k])) it.cen[k] = 0.0f; }  // (sort keys must be ordered)
                 if (node.prim_count <= threshold) { it.ref = LeafRef(node.first_index, node.prim_count); it.weight = (float)node.prim_count; }
                 else
                 {
@@ -665,7 +669,7 @@ int CheckAccelHost(const AccelHost& a, const RtBVHNode* nodes, uint32_t node_cou
     auto bounds = [&](auto&& self, uint32_t ref) -> DBox
     {
         DBox b{ { 1e300, 1e300, 1e300 }, { -1e300, -1e300, -1e300 } };
-        auto grow = [&](const double* lo, const double* hi) { for (int k = 0; k < 3; k++) { b.lo[k] = std::min(b.lo[k], lo[k]); b.hi[k] = std::max(b.hi[k], hi[k]); } };
+        auto grow = [&](const double* lo, const double* hi) { for (int k = 0; k < 3; k++) { b.lo[k] = std::min(b.lo[k], std::max(lo[k], -1.7e38)); b.hi[k] = std::max(b.hi[k], std::min(hi[k], 1.7e38)); } };  // (SetChildBox's clamp)
         const uint32_t off = ref & RT_REF_BYTE_MASK;
         if (ref & RT_LEAF_BIT)
         {
@@ -724,6 +728,7 @@ int CheckAccelHost(const AccelHost& a, const RtBVHNode* nodes, uint32_t node_cou
                 ChildCentreHalf(w, c, ctr, half);
                 double ext = 1e-6;
                 for (int k = 0; k < 3; k++) ext = std::max(ext, cb.hi[k] - cb.lo[k]);
+                if (!(ext < 1e30)) continue;   // clamped infinite bounds: the sampled origins would overflow fp32
                 for (int r = 0; r < 12; r++)
                 {
                     double target[3], od[3];

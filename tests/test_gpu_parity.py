@@ -129,6 +129,38 @@ def test_fresh_random_rays_vs_live_oracle(dev, ref):
         check_ids(ids, ts, low, gt, gid)
 
 
+def test_soup_with_nan_and_infinite_vertices_vs_live_oracle(rt, torch_cuda, ref):
+    """Degenerate input as the domain has it: a soup in which some vertices are NaN or infinite. BVH.cpp leaves what it cannot order
+    in fat leaves with NaN / infinite boxes; the re-layout stores infinite bounds as +-1.7e38 and NaN bounds as an empty box. The
+    product traversal, the reference-order traversal and the unmodified reference on the host must agree on every ray (t bit for
+    bit, same hit / miss; ids under the lowest-id rule can only move to a lower id at the same t)."""
+    rng = np.random.default_rng(3)
+    scene = rt.Scene(None)
+    m = scene.add_material(albedo=(0.5, 0.5, 0.5))
+    for i in range(3000):
+        c = rng.uniform(-10, 10, 3); e = rng.normal(size=(3, 3))
+        p = [c + e[k] for k in range(3)]
+        if i % 97 == 0:
+            p[1] = np.array([np.nan, 1.0, 2.0])
+        if i % 101 == 0:
+            p[2] = np.array([np.inf, 1.0, -np.inf])
+        scene.add_triangle(*p, m)
+    scene.build_bvh()
+    d = gpu_util.DeviceScene(rt, torch_cuda, 64, 48, ((0, 0, -30), 0.0, 0.0), env=False, scene=scene)
+    n = 20000
+    o = rng.uniform(-14, 14, (n, 3)).astype(np.float32)
+    dirs = rng.normal(size=(n, 3)).astype(np.float32)
+    rays = np.concatenate([o, dirs], 1)
+    a = scene.arrays()
+    gid, gt = ref.trace_rays(util.raw(a["vertices"]), util.raw(a["faces"]), util.raw(a["nodes"]), a["face_indices"], util.raw(a["spheres"]), rays, False)
+    assert (gid != 0xFFFFFFFF).mean() > 0.5
+    for variant in (0, 1):
+        ids, ts = d.trace_rays(rays, False, variant)
+        assert np.array_equal(ts.view(np.uint32), gt.view(np.uint32)), (variant, int((ts.view(np.uint32) != gt.view(np.uint32)).sum()))
+        moved = ids != gid
+        assert (ids[moved] < gid[moved]).all() and moved.mean() < 0.01
+
+
 def edge_aimed_rays(scene_arrays, n=60000, seed=7):
     """Rays aimed exactly AT bunny vertices and at points ON bunny edges (half of them a hair beside), half unit-length."""
     a = scene_arrays

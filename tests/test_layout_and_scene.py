@@ -219,6 +219,30 @@ def test_own_topology_over_the_reference_leaves(rt, bunny, monkeypatch):
     assert list(info)[:2] == own[:2] and info[2] + 2 <= 32
 
 
+def test_relayout_of_scenes_with_nan_and_infinite_vertices(rt):
+    """BVH.cpp never splits what it cannot order, so NaN / infinite vertices end up in fat leaves with NaN / infinite boxes. The re-layout
+    must come back (it used to recurse without end in the fat leaf's SAH sweep when no split had a finite cost) and pass the host check:
+    infinite bounds are stored as +-1.7e38, NaN bounds as an empty box (no ray passes a NaN box in the reference either)."""
+    rng = np.random.default_rng(3)
+    for mode in ("nan", "inf", "both"):
+        scene = rt.Scene(None)
+        for i in range(3000):
+            c = rng.uniform(-10, 10, 3); e = rng.normal(size=(3, 3))
+            p = [c + e[k] for k in range(3)]
+            if mode in ("nan", "both") and i % 97 == 0:
+                p[1] = np.array([np.nan, 1.0, 2.0])
+            if mode in ("inf", "both") and i % 101 == 0:
+                p[2] = np.array([np.inf, 1.0, -np.inf])
+            scene.add_triangle(*p, 0)
+        scene.build_bvh()
+        a = scene.arrays()
+        info = (C.c_uint64 * 4)()
+        r = rt.lib().rt_accel_check_host(rt.ptr(a["nodes"]), len(a["nodes"]), rt.ptr(a["face_indices"]), rt.ptr(a["faces"]), len(a["faces"]),
+                                         rt.ptr(a["vertices"]), len(a["vertices"]), 0, info)
+        assert r == 0, (mode, rt.lib().rt_last_error())
+        assert info[2] + 2 <= 64
+
+
 def test_golden_hashes(rt, bunny):
     """Runs everywhere (no /root/reference needed): arrays hash to what the GLM + BVH.cpp build produced."""
     h = json.load(open(os.path.join(util.GOLDEN, "scene_hashes.json")))

@@ -55,11 +55,12 @@ namespace
         float c[3], h[3];
         for (int k = 0; k < 3; k++)
         {   // [c - h, c + h] in exact arithmetic holds [lo, hi]; h carries the 2^-21 the kernel's rounding of h * |1/d| needs
-            // (infinite bounds - a vertex at infinity - become +-1.7e38: everything the kernels can reach lies inside, and centre and
-            // half extent stay finite)
-            const double lo = std::max((double)b.lo[k], -1.7e38), hi = std::min((double)b.hi[k], 1.7e38);
-            c[k] = (float)(0.5 * (lo + hi));
+            const double lo = b.lo[k], hi = b.hi[k];
             if (!(lo <= hi)) { c[k] = 0.0f; h[k] = -1e30f; continue; }  // empty box: exit far before entry, never hit
+            // a bound at infinity (a vertex at infinity) or beyond 1e30: the axis does not constrain - centre 0, half extent 1e30, so that
+            // mid = -o / d stays finite and entry / exit go to -+ huge (a huge CENTRE would overflow mid and turn the test into NaN = miss)
+            if (!(lo > -1e30 && hi < 1e30)) { c[k] = 0.0f; h[k] = 1e30f; continue; }
+            c[k] = (float)(0.5 * (lo + hi));
             const double need = std::max(hi - (double)c[k], (double)c[k] - lo) * (1.0 + 4.8e-7) + 1e-37;
             float hf = (float)need;
             if ((double)hf < need) hf = std::nextafter(hf, INFINITY);
@@ -556,8 +557,26 @@ int BuildAccelHost(const RtBVHNode* nodes, uint32_t node_count, const uint32_t* 
     lap("gather records");
     Builder builder{ nodes, node_count, fat_leaf_threshold, out, {}, {}, 0 };
     const char* topology = std::getenv("B200RT_TOPOLOGY");
-    if (topology && !std::strcmp(topology, "ref"))
-    {   // the reference's own midpoint-split topology (A/B switch)
+    // The own tree rests on one property of the reference's: every inner box holds its children's boxes, so a ray that passes a leaf's
+    // box passes all of its ancestors' (the slab test is monotone in the box). BVH.cpp's UpdateBounds gives that for finite vertices;
+    // NaN or infinite vertices can break it (a NaN bound fails every comparison: the reference never enters such a node, whatever
+    // lies below). Then the reference's own topology is kept, boxes as they are.
+    bool nested = true;
+    for (uint32_t n = 0; n < node_count && nested; n++)
+    {
+        const RtBVHNode& p = nodes[n];
+        const float b[6] = { p.bounds_min.x, p.bounds_min.y, p.bounds_min.z, p.bounds_max.x, p.bounds_max.y, p.bounds_max.z };
+        for (float v : b) if (!std::isfinite(v)) nested = false;
+        if (p.prim_count || !nested) continue;
+        for (uint32_t c = p.first_index; c < p.first_index + 2 && c < node_count; c++)
+        {
+            const RtBVHNode& q = nodes[c];
+            if (!(p.bounds_min.x <= q.bounds_min.x && p.bounds_min.y <= q.bounds_min.y && p.bounds_min.z <= q.bounds_min.z &&
+                  p.bounds_max.x >= q.bounds_max.x && p.bounds_max.y >= q.bounds_max.y && p.bounds_max.z >= q.bounds_max.z)) nested = false;
+        }
+    }
+    if (!nested || (topology && !std::strcmp(topology, "ref")))
+    {   // the reference's own midpoint-split topology (A/B switch; scenes whose boxes do not nest)
         out.wide.reserve(node_count / 2 + 16);
         out.root_ref = builder.Emit(0, 0);
     }
@@ -669,7 +688,7 @@ int CheckAccelHost(const AccelHost& a, const RtBVHNode* nodes, uint32_t node_cou
     auto bounds = [&](auto&& self, uint32_t ref) -> DBox
     {
         DBox b{ { 1e300, 1e300, 1e300 }, { -1e300, -1e300, -1e300 } };
-        auto grow = [&](const double* lo, const double* hi) { for (int k = 0; k < 3; k++) { b.lo[k] = std::min(b.lo[k], std::max(lo[k], -1.7e38)); b.hi[k] = std::max(b.hi[k], std::min(hi[k], 1.7e38)); } };  // (SetChildBox's clamp)
+        auto grow = [&](const double* lo, const double* hi) { for (int k = 0; k < 3; k++) { b.lo[k] = std::min(b.lo[k], std::max(lo[k], -1e30)); b.hi[k] = std::max(b.hi[k], std::min(hi[k], 1e30)); } };  // (SetChildBox: beyond 1e30 = unconstrained)
         const uint32_t off = ref & RT_REF_BYTE_MASK;
         if (ref & RT_LEAF_BIT)
         {

@@ -143,7 +143,9 @@ __device__ __forceinline__ bool tri_test(Vec3 o, Vec3 nd, float4 r0, float4 r1, 
 // used by the path tracer so shading picks the same duplicate the reference does).
 __device__ __forceinline__ bool accept(float t, uint32_t key, const HitRecord& h)
 {
-    if (t > h.t || t < 0.0f) return false;
+    // (a NaN t - a vertex at infinity: e2 . q = inf - inf - is no hit. The reference's `>=` / `<` let a NaN distance through, after which
+    // every comparison with it is false and what it returns is whatever it visits last; no order-independent rule can mirror that.)
+    if (!(t <= h.t) || t < 0.0f) return false;
     return t < h.t || (key < h.key && !(h.id & RT_SPHERE_ID_BIT));  // a sphere at the same t keeps the hit (:62, `>=`)
 }
 

@@ -111,7 +111,7 @@ def scaled_scene(rt, which, env=True, grid=10):
 
 def raw(a):
     """uint8 [n, itemsize] view of a structured array (what oracle/ref_oracle.py takes)."""
-    return np.ascontiguousarray(a).view(np.uint8).reshape(len(a), -1)
+    return np.ascontiguousarray(a).view(np.uint8).reshape(len(a), a.dtype.itemsize)
 
 
 # ---- DDS containers for the general loader tests (SURVEY 8f.3) ------------------------------------------------------------

@@ -152,7 +152,7 @@ class ClockSampler:
         try:
             self.f = open(self.path, "w")
             cmd = ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"]
-            if index is not None:   # None = every GPU of the node (multi-rank runs: the step time is the slowest rank's)
+            if index is not None:   # one GPU, or a comma-separated list (multi-rank runs: the step time is the slowest rank's)
                 cmd += ["-i", str(index)]
             self.proc = subprocess.Popen(cmd, stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
@@ -322,7 +322,12 @@ def run_b200_arm(a):
     torch.cuda.synchronize()
     d.counter.zero_()
     uuid = str(torch.cuda.get_device_properties(local).uuid)
-    sampler = ClockSampler((uuid if uuid.startswith("GPU-") else "GPU-" + uuid) if world == 1 else None) if rank == 0 else None
+    uuid = uuid if uuid.startswith("GPU-") else "GPU-" + uuid
+    if world > 1:   # the GPUs of THIS job (idle GPUs of the node sit at 120 MHz and must not enter the median)
+        uuids = [None] * world
+        dist.all_gather_object(uuids, uuid, group=host_group)
+        uuid = ",".join(uuids)
+    sampler = ClockSampler(uuid) if rank == 0 else None
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
     wall0 = time.perf_counter()
     for k in range(a.steps):

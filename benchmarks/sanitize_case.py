@@ -1,5 +1,5 @@
-"""Smallest run that touches every kernel once (for compute-sanitizer): primary/rays queries (3 variants), RNG init/draw,
-path tracing variants 0/1/2, AO, tone-map, the facade and its RenderToHost."""
+"""Smallest run that touches every kernel once (for compute-sanitizer): primary/rays queries (both variants), RNG init/draw,
+path tracing variants 0/1/2/3/10, AO, tone-map, the facade and its RenderToHost."""
 import os
 import sys
 
@@ -22,13 +22,15 @@ for v in (0, 1):
     d.trace_primary(1, v)
 rays = np.random.default_rng(0).normal(size=(5000, 6)).astype(np.float32)
 rays[:, :3] = rays[:, :3] * 10 + (30, 0, 20)
-for v in (0, 1, 2):
+for v in (0, 1):
     d.trace_rays(rays, True, v)
 work = torch.zeros(2, dtype=torch.int64, device="cuda")
 from cuda_raytracing_b200.api import process_ex
-for v in (0, 1):
+for v in (0, 1, 10):
     d.process(0, spp=3, bounces=4, variant=v, write_last=1)
-process_ex(d.surface, d.last, W, H, d.pitch, 0, d.gpu, d.accel, spp=1, bounces=4, variant=2, ray_counter=d.counter, work_counters=work)
+    d.process(1, spp=2, bounces=4, variant=v, write_last=1)   # second launch: the tile schedule reads the first one's costs
+for v in (2, 3):
+    process_ex(d.surface, d.last, W, H, d.pitch, 0, d.gpu, d.accel, spp=1, bounces=4, variant=v, ray_counter=d.counter, work_counters=work)
 ao = torch.zeros(W * H, dtype=torch.float32, device="cuda")
 rt.check(rt.lib().rt_ambient_occlusion(d.accel, d.gpu, W, H, 4, rt.ptr(ao), rt.ptr(d.counter), None))
 out = torch.zeros((H, W, 4), dtype=torch.uint8, device="cuda")

@@ -29,7 +29,7 @@ class Mesh:
         check(lib().rt_host_mesh_load_obj_subdivided(_b(obj_path), subdivide, C.byref(h)))
         self.handle = h
 
-    def __del__(self):
+    def __del__(self, _safe_destroy=_safe_destroy):   # bound at definition: module globals are None by the time exit-time destructors run
         if getattr(self, "handle", None):
             _safe_destroy("rt_host_mesh_destroy", self.handle)
             self.handle = None
@@ -56,7 +56,7 @@ class Scene:
         if not self.handle:
             raise RuntimeError("rt_host_scene_create failed")
 
-    def __del__(self):
+    def __del__(self, _safe_destroy=_safe_destroy):   # bound at definition: module globals are None by the time exit-time destructors run
         if getattr(self, "_owned", False) and getattr(self, "handle", None):
             _safe_destroy("rt_host_scene_destroy", self.handle)
             self.handle = None
@@ -148,7 +148,7 @@ class Accel:
     def info(self):
         return _accel_info(self.handle)
 
-    def __del__(self):
+    def __del__(self, _safe_destroy=_safe_destroy):   # bound at definition: module globals are None by the time exit-time destructors run
         if getattr(self, "handle", None):
             _safe_destroy("rt_accel_destroy", self.handle)
             self.handle = None
@@ -164,7 +164,7 @@ class EnvMap:
     def texture(self):
         return lib().rt_envmap_texture(self.handle)
 
-    def __del__(self):
+    def __del__(self, _safe_destroy=_safe_destroy):   # bound at definition: module globals are None by the time exit-time destructors run
         if getattr(self, "handle", None):
             _safe_destroy("rt_envmap_destroy", self.handle)
             self.handle = None
@@ -214,7 +214,7 @@ class Tracer:
     def ray_count(self):
         return lib().rt_host_tracer_ray_count(self.handle)
 
-    def __del__(self):
+    def __del__(self, _safe_destroy=_safe_destroy):   # bound at definition: module globals are None by the time exit-time destructors run
         if getattr(self, "handle", None):
             _safe_destroy("rt_host_tracer_destroy", self.handle)
             self.handle = None
@@ -252,7 +252,7 @@ class MultiTracer:
     def ray_count(self):
         return lib().rt_host_multi_tracer_ray_count(self.handle)
 
-    def __del__(self):
+    def __del__(self, _safe_destroy=_safe_destroy):   # bound at definition: module globals are None by the time exit-time destructors run
         if getattr(self, "handle", None):
             _safe_destroy("rt_host_multi_tracer_destroy", self.handle)
             self.handle = None

@@ -12,6 +12,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include "b200rt.h"
 
 namespace
@@ -186,11 +187,13 @@ namespace
         uint32_t fat_depth = 0;
 
         // reference leaves in visiting order; fat ones get their private sub-tree (appended to out.wide) first
-        void CollectLeaves()
+        // One walk of the reference tree: its leaves in visiting order (validated), its depth.
+        std::vector<uint32_t> leaf_nodes;
+        void WalkReference()
         {
             std::vector<std::pair<uint32_t, uint32_t>> stack; stack.push_back({ 0u, 0u });
             uint64_t visited = 0;
-            while (!stack.empty() && !error)
+            while (!stack.empty())
             {
                 const auto [n, depth] = stack.back(); stack.pop_back();
                 if (n >= node_count || ++visited > node_count) { error = RT_E_INVALID; return; }
@@ -202,25 +205,40 @@ namespace
                     stack.push_back({ node.first_index + 1, depth + 1 }); stack.push_back({ node.first_index, depth + 1 });
                     continue;
                 }
-                out.ref_leaf_count++;
                 if ((uint64_t)node.first_index + node.prim_count > out.tris.size()) { error = RT_E_INVALID; return; }
+                leaf_nodes.push_back(n);
+            }
+        }
+
+        // items[] from leaf_nodes[]; fat leaves get their private sub-tree (appended to out.wide, which already holds the own tree's nodes)
+        void CollectLeaves()
+        {
+            const int64_t count = (int64_t)leaf_nodes.size();
+            items.resize(leaf_nodes.size());
+            out.ref_leaf_count = (uint32_t)leaf_nodes.size();
+#pragma omp parallel for schedule(static) if (count > 100000)
+            for (int64_t i = 0; i < count; i++)
+            {
+                const uint32_t n = leaf_nodes[i];
+                const RtBVHNode& node = nodes[n];
                 for (uint32_t s = node.first_index; s < node.first_index + node.prim_count; s++) out.tris[s].ref_leaf = n;
-                Item it;
+                Item& it = items[i];
                 it.box = FromNode(node);
                 for (int k = 0; k < 3; k++) { it.cen[k] = 0.5f * it.box.lo[k] + 0.5f * it.box.hi[k]; if (!std::isfinite(it.cen[k])) it.cen[k] = 0.0f; }  // (sort keys must be ordered)
-                if (node.prim_count <= threshold) { it.ref = LeafRef(node.first_index, node.prim_count); it.weight = (float)node.prim_count; }
-                else
-                {
-                    out.fat_leaf_count++;
-                    const uint32_t before = out.wide_depth;
-                    out.wide_depth = 0;
-                    Box unused;
-                    it.ref = BuildSub(node.first_index, node.prim_count, 0, unused);
-                    fat_depth = std::max(fat_depth, out.wide_depth);
-                    out.wide_depth = before;
-                    it.weight = 2.0f * std::log2((float)node.prim_count) + 4.0f;  // expected steps inside the sub-tree
-                }
-                items.push_back(it);
+                it.ref = LeafRef(node.first_index, std::min(node.prim_count, threshold)); it.weight = (float)node.prim_count;
+            }
+            for (int64_t i = 0; i < count; i++)
+            {
+                const RtBVHNode& node = nodes[leaf_nodes[i]];
+                if (node.prim_count <= threshold) continue;
+                out.fat_leaf_count++;
+                const uint32_t before = out.wide_depth;
+                out.wide_depth = 0;
+                Box unused;
+                items[i].ref = BuildSub(node.first_index, node.prim_count, 0, unused);
+                fat_depth = std::max(fat_depth, out.wide_depth);
+                out.wide_depth = before;
+                items[i].weight = 2.0f * std::log2((float)node.prim_count) + 4.0f;  // expected steps inside the sub-tree
             }
         }
 
@@ -242,7 +260,7 @@ namespace
                 return lo + n / 2;
             };
             if (balanced || n == 2) return median();
-            if (n <= 1024)
+            if (n <= 1024)   // (binned from 8, 32 or 128 items on gives the same cost to three digits and the same build time)
             {   // full sweep on the three axes
                 float best_cost = 3.4e38f; int best_axis = -1, sorted_axis = -1; uint32_t best_split = 0;
                 std::vector<float> right_area(n), right_weight(n);
@@ -265,21 +283,39 @@ namespace
                 if (best_axis != sorted_axis) std::stable_sort(it, it + n, [&](const Item& a, const Item& b) { return a.cen[best_axis] < b.cen[best_axis]; });
                 return lo + best_split;
             }
-            // binned
+            // binned: one pass over the items fills the bins of all three axes; large ranges in chunks that the team's idle threads take
+            // (the top levels of a big tree would otherwise run on one thread while the others wait for tasks)
             constexpr int kBins = 64;
+            struct Bins { Box box[3][kBins]; float weight[3][kBins]; uint32_t count[3][kBins]; };
+            auto clear = [](Bins& b) { for (int a = 0; a < 3; a++) for (int k = 0; k < kBins; k++) { b.box[a][k] = EmptyBox(); b.weight[a][k] = 0; b.count[a][k] = 0; } };
+            float scale3[3];
+            for (int a = 0; a < 3; a++) { const float extent = cb.hi[a] - cb.lo[a]; scale3[a] = extent > 0 ? (float)kBins / extent : 0.0f; }
+            auto fill = [&](Bins& b, uint32_t from, uint32_t to)
+            {
+                for (uint32_t i = from; i < to; i++)
+                    for (int a = 0; a < 3; a++)
+                    {
+                        const int k = std::min(kBins - 1, std::max(0, (int)((it[i].cen[a] - cb.lo[a]) * scale3[a])));
+                        Grow(b.box[a][k], it[i].box); b.weight[a][k] += it[i].weight; b.count[a][k]++;
+                    }
+            };
+            std::unique_ptr<Bins> bins(new Bins); clear(*bins);
+            if (n < (1u << 18)) fill(*bins, 0, n);
+            else
+            {
+                const int chunks = 64;
+                std::vector<Bins> part(chunks);
+#pragma omp taskloop default(shared) grainsize(1)
+                for (int c = 0; c < chunks; c++) { clear(part[c]); fill(part[c], (uint32_t)((uint64_t)n * c / chunks), (uint32_t)((uint64_t)n * (c + 1) / chunks)); }
+                for (int c = 0; c < chunks; c++)
+                    for (int a = 0; a < 3; a++) for (int k = 0; k < kBins; k++)
+                        if (part[c].count[a][k]) { Grow(bins->box[a][k], part[c].box[a][k]); bins->weight[a][k] += part[c].weight[a][k]; bins->count[a][k] += part[c].count[a][k]; }
+            }
             float best_cost = 3.4e38f; int best_axis = -1, best_plane = 0;
             for (int axis = 0; axis < 3; axis++)
             {
-                const float extent = cb.hi[axis] - cb.lo[axis];
-                if (!(extent > 0)) continue;
-                const float scale = (float)kBins / extent;
-                Box bin_box[kBins]; float bin_weight[kBins]; uint32_t bin_count[kBins];
-                for (int b = 0; b < kBins; b++) { bin_box[b] = EmptyBox(); bin_weight[b] = 0; bin_count[b] = 0; }
-                for (uint32_t i = 0; i < n; i++)
-                {
-                    const int b = std::min(kBins - 1, std::max(0, (int)((it[i].cen[axis] - cb.lo[axis]) * scale)));
-                    Grow(bin_box[b], it[i].box); bin_weight[b] += it[i].weight; bin_count[b]++;
-                }
+                if (!(cb.hi[axis] - cb.lo[axis] > 0)) continue;
+                const Box* bin_box = bins->box[axis]; const float* bin_weight = bins->weight[axis]; const uint32_t* bin_count = bins->count[axis];
                 float right_area[kBins], right_weight[kBins]; uint32_t right_count[kBins];
                 Box acc = EmptyBox(); float w = 0; uint32_t c = 0;
                 for (int b = kBins; b-- > 0;) { if (bin_count[b]) Grow(acc, bin_box[b]); w += bin_weight[b]; c += bin_count[b]; right_area[b] = HalfArea(acc); right_weight[b] = w; right_count[b] = c; }
@@ -385,12 +421,13 @@ namespace
                 order.clear();
                 for (uint32_t i = 0; i < tree.size(); i++) if (i != tree_root && tree[i].parent != tree_root) order.push_back({ HalfArea(tree[i].box), i });
                 for (uint32_t i = 0; i < items.size(); i++) if (item_parent[i] != tree_root) order.push_back({ HalfArea(items[i].box), kItem | i });
-                std::stable_sort(order.begin(), order.end(), [](const auto& a, const auto& b) { return a.first > b.first; });
+                auto larger = [](const std::pair<float, uint32_t>& a, const std::pair<float, uint32_t>& b) { return a.first > b.first || (a.first == b.first && a.second < b.second); };
                 // every node of a tree of up to 2^18 leaves (0.4 s on the bunny scene's 69 376); beyond that the 4 096 largest - nearly all of
                 // the gain sits there (walls, floors, the boxes of whole objects: bunny scene 6.43 -> 5.63 expected node steps from the 100
                 // largest alone, 5.61 from all), and the search per node does not grow with the scene
                 const size_t most = std::getenv("B200RT_REINSERT_MAX") ? (size_t)std::atoll(std::getenv("B200RT_REINSERT_MAX")) : (items.size() <= (1u << 18) ? (size_t)-1 : (size_t)4096);
-                if (order.size() > most) order.resize(most);
+                if (order.size() > most) { std::nth_element(order.begin(), order.begin() + most, order.end(), larger); order.resize(most); }
+                std::sort(order.begin(), order.end(), larger);
                 for (const auto& entry : order)
                 {
                     const uint32_t n = entry.second;
@@ -446,8 +483,11 @@ namespace
                 if (!(tree[t].child[1] & kItem)) stack.push_back(tree[t].child[1]);
                 if (!(tree[t].child[0] & kItem)) stack.push_back(tree[t].child[0]);
             }
-            for (uint32_t t : sequence)
+            const int64_t count = (int64_t)sequence.size();
+#pragma omp parallel for schedule(static) if (count > 100000)
+            for (int64_t i = 0; i < count; i++)
             {
+                const uint32_t t = sequence[i];
                 WideNode& w = out.wide[index[t]];
                 for (int c = 0; c < 2; c++)
                 {
@@ -462,24 +502,18 @@ namespace
         // Root reference of the own-topology tree (RT_SENTINEL + error on failure).
         uint32_t BuildOwnTopology()
         {
-            // reserve the own tree's nodes at the front (root = wide[0]); fat-leaf sub-trees are appended behind them
-            uint32_t leaves = 0;
-            {
-                std::vector<uint32_t> stack; stack.push_back(0);
-                uint64_t visited = 0;
-                while (!stack.empty())
-                {
-                    const uint32_t n = stack.back(); stack.pop_back();
-                    if (n >= node_count || ++visited > node_count) { error = RT_E_INVALID; return RT_SENTINEL; }
-                    if (nodes[n].prim_count) leaves++;
-                    else { stack.push_back(nodes[n].first_index); stack.push_back(nodes[n].first_index + 1); }
-                }
-            }
-            out.wide.assign(leaves > 1 ? leaves - 1 : 0, WideNode{});
-            items.reserve(leaves);
-            CollectLeaves();
+            const bool timing = std::getenv("B200RT_BVH_TIMING") != nullptr;
+            auto clock0 = std::chrono::steady_clock::now();
+            auto lap = [&](const char* what) { if (!timing) return; auto now = std::chrono::steady_clock::now(); std::fprintf(stderr, "[accel]   %-18s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(now - clock0).count()); clock0 = now; };
+            WalkReference();
             if (error) return RT_SENTINEL;
-            if (items.size() != leaves) { error = RT_E_INVALID; return RT_SENTINEL; }
+            const uint32_t leaves = (uint32_t)leaf_nodes.size();
+            // the own tree's nodes at the front (root = wide[0]); fat-leaf sub-trees are appended behind them
+            out.wide.assign(leaves > 1 ? leaves - 1 : 0, WideNode{});
+            lap("walk reference tree");
+            CollectLeaves();
+            lap("collect leaves");
+            if (error) return RT_SENTINEL;
             if (leaves == 1) return items[0].ref;
             if (CeilLog2(leaves) + fat_depth + 4 > RT_STACK_SIZE) { error = RT_E_DEPTH; return RT_SENTINEL; }
             const uint32_t depth_limit = RT_STACK_SIZE - 3 - fat_depth;
@@ -489,7 +523,9 @@ namespace
 #pragma omp parallel
 #pragma omp single
             BuildOwn(0, leaves, 0, 0, depth_limit);
+            lap("SAH splits");
             for (uint32_t i = leaves - 1; i-- > 0;) tree[i].box = Union(BoxOf(tree[i].child[0]), BoxOf(tree[i].child[1]));  // children follow parents
+            lap("inner boxes");
             const int passes = std::getenv("B200RT_REINSERT") ? std::atoi(std::getenv("B200RT_REINSERT")) : 1;
             if (passes > 0 && leaves > 3)
             {
@@ -498,8 +534,10 @@ namespace
                 Optimize(passes, depth_limit);
                 if (std::getenv("B200RT_BVH_TIMING")) std::fprintf(stderr, "[accel] reinsertion: area sum %.4g -> %.4g, depth %u\n", cost0, TreeCost(), TreeDepth());
                 if (TreeDepth() + fat_depth + 3 > RT_STACK_SIZE) { tree = before; item_parent = before_parent; tree_root = 0; }
+                lap("reinsertion");
             }
             EmitTree();
+            lap("emit wide nodes");
             return 0;
         }
 

@@ -211,21 +211,26 @@ def csrc_hash():
     import hashlib
     h = hashlib.sha1()
     d = os.path.join(ROOT, "cuda-raytracing_b200", "csrc")
-    # what the megakernel is compiled from, and the builder of the tree it walks (the tree decides the instructions per ray)
-    for name in ("accel.h", "accel_build.cpp", "kernels.h", "pathtrace.cu", "pathtrace_common.cuh", "rng.cuh", "shade.cuh", "traverse.cuh"):
+    # what the megakernel is compiled from (the tree it walks is tied to a capture by its measured steps per ray, load_capture)
+    for name in ("accel.h", "kernels.h", "pathtrace.cu", "pathtrace_common.cuh", "rng.cuh", "shade.cuh", "traverse.cuh"):
         h.update(name.encode()); h.update(open(os.path.join(d, name), "rb").read())
     return h.hexdigest()[:16]
 
 
-def load_capture(key):
+def load_capture(key, node_steps_per_ray=None, tri_tests_per_ray=None):
     """One entry of profiles/traffic.json (written by benchmarks/update_traffic.py from an ncu --set full report), or None when it
-    was captured on other device sources than the ones in this tree."""
+    was captured on other device sources than the ones in this source tree, or on another BVH: the capture records the wide-node
+    steps and triangle tests per ray that the captured launch's tree gave (variant 3 counters of the same bench command), and this
+    run's live counters must agree - a different tree means a different instruction count per ray."""
     try:
         cap = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[key]
     except Exception:
         return None, "no capture in profiles/traffic.json"
     if cap.get("csrc_hash") != csrc_hash():
         return None, f"capture in profiles/traffic.json was taken on csrc {cap.get('csrc_hash')}, tree is {csrc_hash()}: re-run benchmarks/update_traffic.py"
+    for name, live in (("node_steps_per_ray", node_steps_per_ray), ("tri_tests_per_ray", tri_tests_per_ray)):
+        if live is not None and (cap.get(name) is None or abs(cap[name] - live) > 1e-4 * live):
+            return None, f"capture in profiles/traffic.json was taken on a BVH with {name} = {cap.get(name)}, this run's has {live}: re-run benchmarks/update_traffic.py"
     return cap, None
 
 
@@ -391,7 +396,7 @@ def run_b200_arm(a):
     # L2 bytes per launch come from the committed ncu capture of this exact launch (never measured under bench); time and clock are live.
     cap, cap_note = (None, "not the captured launch shape")
     if a.variant == 0 and (a.width, a.height, a.spp_per_launch, a.bounces, a.pose) == (1920, 1080, 64, 4, "poseB"):
-        cap, cap_note = load_capture("pathtrace_megakernel")
+        cap, cap_note = load_capture("pathtrace_megakernel", steps_per_ray, tests_per_ray)
     alg_ref = rays_per_launch * bytes_per_ray + px * 80.0
     alg_prod = rays_per_launch * bytes_per_ray_product + px * 80.0
     roofline = {"bound": "issue", "achieved": None, "peak": peak_ginst, "unit": "G warp-inst/s", "frac": None, "traffic": None,

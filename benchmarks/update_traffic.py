@@ -24,6 +24,15 @@ def main(rep, note):
         return v * {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9}.get(u, 1)
 
 
+    # the bench line of the same command, run without ncu just before the capture (gpu_bench_and_profile.sh: <tag>_plain2.log): the
+    # steps per ray of the tree the captured launch walked
+    steps = tests = None
+    plain = rep.replace("_megakernel.ncu-rep", "_plain2.log")
+    if os.path.exists(plain):
+        for line in open(plain):
+            if line.startswith("{"):
+                r = json.loads(line)["roofline"]
+                steps, tests = r["node_steps_per_ray_product_order"], r["tri_tests_per_ray_product_order"]
     path = os.path.join(ROOT, "profiles", "traffic.json")
     sys.path.insert(0, ROOT)
     import bench
@@ -38,6 +47,7 @@ def main(rep, note):
         "issue_active_pct": round(val("smsp__issue_active.avg.pct_of_peak_sustained_active"), 2),
         "duration_under_ncu": d["gpu__time_duration.sum"] + " " + units[hdr.index("gpu__time_duration.sum")],
         "csrc_hash": bench.csrc_hash(),
+        "node_steps_per_ray": steps, "tri_tests_per_ray": tests,
         "source": note,
     }
     json.dump(t, open(path, "w"), indent=1)

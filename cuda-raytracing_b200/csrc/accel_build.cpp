@@ -418,6 +418,7 @@ namespace
             std::vector<std::pair<float, uint32_t>> order;
             for (int pass = 0; pass < passes; pass++)
             {
+                uint64_t visits = 0;
                 order.clear();
                 for (uint32_t i = 0; i < tree.size(); i++) if (i != tree_root && tree[i].parent != tree_root) order.push_back({ HalfArea(tree[i].box), i });
                 for (uint32_t i = 0; i < items.size(); i++) if (item_parent[i] != tree_root) order.push_back({ HalfArea(items[i].box), kItem | i });
@@ -428,8 +429,12 @@ namespace
                 const size_t most = std::getenv("B200RT_REINSERT_MAX") ? (size_t)std::atoll(std::getenv("B200RT_REINSERT_MAX")) : (items.size() <= (1u << 18) ? (size_t)-1 : (size_t)4096);
                 if (order.size() > most) { std::nth_element(order.begin(), order.begin() + most, order.end(), larger); order.resize(most); }
                 std::sort(order.begin(), order.end(), larger);
+                // the branch-and-bound search prunes well in ordinary scenes (bunny scene: 36 nodes looked at per reinsertion) and badly where
+                // everything overlaps everything; largest nodes first, so running out of budget drops the least valuable ones
+                const uint64_t budget = 256ull * order.size() + (1ull << 20);
                 for (const auto& entry : order)
                 {
+                    if (visits > budget) break;
                     const uint32_t n = entry.second;
                     const uint32_t p = ParentOf(n);
                     if (p == tree_root) continue;                     // (the tree changed since the list was made)
@@ -448,6 +453,7 @@ namespace
                     while (!heap.empty())
                     {
                         std::pop_heap(heap.begin(), heap.end()); const Entry e = heap.back(); heap.pop_back();
+                        visits++;
                         if (e.induced + na >= best_cost) break;
                         const Box& xb = BoxOf(e.ref);
                         const float direct = HalfArea(Union(xb, nb));
@@ -466,6 +472,7 @@ namespace
                     Refit(bp);
                 }
                 (void)depth_limit;
+                if (std::getenv("B200RT_BVH_TIMING")) std::fprintf(stderr, "[accel]   reinsertion pass %d: %zu candidates, %llu nodes looked at (budget %llu)\n", pass, order.size(), (unsigned long long)visits, (unsigned long long)budget);
             }
         }
 

@@ -129,6 +129,37 @@ def test_fresh_random_rays_vs_live_oracle(dev, ref):
         check_ids(ids, ts, low, gt, gid)
 
 
+@pytest.mark.parametrize("count,size", [(1, 1.0), (2, 1.0), (3, 4.0), (60, 0.3), (3000, 1.0), (3000, 6.0), (40000, 0.2)])
+def test_random_soups_vs_live_oracle(rt, torch_cuda, ref, count, size):
+    """The product's own tree (SAH + reinsertion over the reference's leaves, with fat-leaf sub-trees where BVH.cpp could not split) on
+    scenes that are not the bunny: triangle soups from one triangle to 40 000, sparse to everything-overlaps-everything. Product
+    traversal and reference-order traversal against the unmodified reference's GetRayHit on the host: t bit for bit on every ray, ids
+    only ever lower at an exact tie."""
+    rng = np.random.default_rng(1000 + count + int(size * 10))
+    scene = rt.Scene(None)
+    m = scene.add_material(albedo=(0.5, 0.5, 0.5))
+    c = rng.uniform(-10, 10, (count, 3)); e = rng.normal(size=(count, 3, 3)) * size
+    for i in range(count):
+        scene.add_triangle(c[i] + e[i, 0], c[i] + e[i, 1], c[i] + e[i, 2], m)
+    scene.build_bvh()
+    d = gpu_util.DeviceScene(rt, torch_cuda, 64, 48, ((0, 0, -30), 0.0, 0.0), env=False, scene=scene)
+    n = 30000
+    o = rng.uniform(-16, 16, (n, 3)).astype(np.float32)
+    target = (c[rng.integers(0, count, n)] + rng.normal(size=(n, 3)) * size * 0.5).astype(np.float32)   # towards the triangles
+    dirs = np.where(rng.uniform(size=(n, 1)) < 0.7, target - o, rng.normal(size=(n, 3))).astype(np.float32)
+    dirs[::3] /= np.linalg.norm(dirs[::3], axis=1, keepdims=True)
+    rays = np.concatenate([o, dirs], 1)
+    rays[:64, 3:] = 0; rays[:64, 3 + (np.arange(64) % 3)] = np.where(np.arange(64) % 2, 1.0, -1.0)   # axis-parallel
+    a = scene.arrays()
+    gid, gt = ref.trace_rays(util.raw(a["vertices"]), util.raw(a["faces"]), util.raw(a["nodes"]), a["face_indices"], util.raw(a["spheres"]), rays, False)
+    assert (gid != 0xFFFFFFFF).mean() > 0.03   # (4 % for the one-triangle scene, 98 % for the dense soup)
+    for variant in (0, 1):
+        ids, ts = d.trace_rays(rays, False, variant)
+        assert np.array_equal(ts.view(np.uint32), gt.view(np.uint32)), (variant, int((ts.view(np.uint32) != gt.view(np.uint32)).sum()))
+        moved = ids != gid
+        assert (ids[moved] < gid[moved]).all() and moved.mean() < 0.02, (variant, float(moved.mean()))
+
+
 @pytest.mark.parametrize("mode", ["nan", "inf", "both"])
 def test_soup_with_nan_and_infinite_vertices(rt, torch_cuda, mode):
     """Degenerate input as the domain has it: a soup in which some vertices are NaN or infinite. BVH.cpp's boxes then hold infinite

@@ -811,6 +811,10 @@ int CheckAccelHost(const AccelHost& a, const RtBVHNode* nodes, uint32_t node_cou
                     bool truth = true;
                     for (int k = 0; k < 3 && truth; k++)
                     {
+                        // a ray that runs INSIDE the plane of a zero-thickness box (an axis-aligned wall: lo == hi, d == 0, o on the plane) is
+                        // not a witness: everything below such a box is triangles in that plane, which the ray sees edge-on (det == 0: no
+                        // hit in the reference either), and the centre form gives it the slab [-h * 1e30, +h * 1e30] around t = 0 with h ~ 1e-37
+                        if (d[k] == 0.0f && cb.lo[k] == cb.hi[k]) { truth = false; continue; }
                         if (d[k] == 0.0f) { truth = (double)o[k] >= cb.lo[k] && (double)o[k] <= cb.hi[k]; continue; }
                         const double ta = (cb.lo[k] - o[k]) / d[k], tb = (cb.hi[k] - o[k]) / d[k];
                         t0 = std::max(t0, std::min(ta, tb)); t1 = std::min(t1, std::max(ta, tb));

@@ -220,6 +220,40 @@ def test_own_topology_over_the_reference_leaves(rt, bunny, monkeypatch):
     assert info[2] < own[2]   # (18 against 21 levels: the limiter did have work to do, and the reinsertion pass, whose result was 24 deep, was undone)
 
 
+def test_relayout_fuzz_through_the_host_check(rt):
+    """120 random soups through BVH.cpp's builder, the re-layout (own SAH tree, fat-leaf sub-trees) and the host check: 1 to 3 000
+    triangles, scene scales 1e-3 to 1e4, triangle sizes 1e-4 to 2 scene units, and the degenerate families - identical centroids (one
+    fat leaf), collinear triangles, everything in one axis-aligned plane (zero-thickness boxes), every triangle four times, a scene
+    1 000 times longer than wide."""
+    rng = np.random.default_rng(11)
+    for case in range(120):
+        n = int(rng.choice([1, 2, 3, 5, 9, 17, 40, 100, 300, 1000, 3000]))
+        kind = case % 6
+        scale = float(rng.choice([1e-3, 0.1, 1.0, 30.0, 1e4]))
+        size = float(rng.choice([1e-4, 0.01, 0.3, 2.0])) * scale
+        c = rng.uniform(-scale, scale, (n, 3)); e = rng.normal(size=(n, 3, 3)) * size
+        if kind == 1:
+            c[:] = c[0]
+        if kind == 2:
+            e[:, 1] = e[:, 0] * 2
+        if kind == 3:
+            c[:, 1] = 0; e[:, :, 1] = 0
+        if kind == 4:
+            c = np.repeat(c[: max(1, n // 4)], 4, axis=0)[:n]; e = np.repeat(e[: max(1, n // 4)], 4, axis=0)[:n]
+        if kind == 5:
+            c[:, 0] *= 1e3
+        scene = rt.Scene(None)
+        for i in range(len(c)):
+            scene.add_triangle(c[i] + e[i, 0], c[i] + e[i, 1], c[i] + e[i, 2], 0)
+        scene.build_bvh()
+        a = scene.arrays()
+        for threshold in (0, 2):
+            info = (C.c_uint64 * 4)()
+            r = rt.lib().rt_accel_check_host(rt.ptr(a["nodes"]), len(a["nodes"]), rt.ptr(a["face_indices"]), rt.ptr(a["faces"]), len(a["faces"]),
+                                             rt.ptr(a["vertices"]), len(a["vertices"]), threshold, info)
+            assert r == 0, (case, n, kind, scale, size, threshold, rt.lib().rt_last_error())
+
+
 def test_relayout_of_scenes_with_nan_and_infinite_vertices(rt):
     """BVH.cpp never splits what it cannot order, so NaN / infinite vertices end up in fat leaves with NaN / infinite boxes. The re-layout
     must come back (it used to recurse without end in the fat leaf's SAH sweep when no split had a finite cost) and pass the host check:

@@ -235,7 +235,7 @@ def test_relayout_fuzz_through_the_host_check(rt):
         if kind == 1:
             c[:] = c[0]
         if kind == 2:
-            e[:, 1] = e[:, 0] * 2
+            e[::2, 1] = e[::2, 0] * 2; e[::2, 2] = e[::2, 0] * 3   # every other triangle has its three vertices on one line
         if kind == 3:
             c[:, 1] = 0; e[:, :, 1] = 0
         if kind == 4:
